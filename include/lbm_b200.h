@@ -1,0 +1,177 @@
+/*
+ * lbm_b200.h -- C ABI of the B200-native D2Q9 BGK timestep path.
+ *
+ * Drop-in boundary for the hot path of jodavies/latticeboltzmann
+ * (src/latticeboltzmann.c, "LB.c").  The reference has no plugin layer; its
+ * boundary is the prototype block LB.c:85-123.  Every entry point below names
+ * the reference function (file:line) it replaces.  Plain pointers and sizes
+ * only; no CUDA or torch types cross this boundary.
+ *
+ * Precision is chosen at compile time exactly as in the reference
+ * (LB.c:59-65): include prec_double_cuda.h or prec_float_cuda.h first, link
+ * against liblbm_b200_dp.so or liblbm_b200_sp.so.  Both libraries export the
+ * same symbol names; lbm_sizeof_real() lets a caller check the pairing.
+ *
+ * Host array layout accepted by upload/download is the reference's
+ * (LB.c:71-72): f[s][i][j] at s*nx*ldy + i*ldy + j with j contiguous, walls
+ * as char 0/1 with the same row stride ldy (= NYPADDED).  Packing the mask to
+ * one bit per site and padding rows to 128 B happens inside.
+ *
+ * There is no CPU fallback: every call fails with LBM_ERR_CUDA when no
+ * sm_100 device is usable.
+ */
+#ifndef LBM_B200_H
+#define LBM_B200_H
+
+#include <stddef.h>
+
+#ifndef LBM_PREC_SELECTED
+#error "include prec_double_cuda.h or prec_float_cuda.h before lbm_b200.h (cf. LB.c:59-65)"
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lbm_ctx lbm_ctx; /* one slab of the lattice on one GPU */
+
+enum {
+	LBM_OK = 0,
+	LBM_ERR_ARG = 1,    /* bad argument (odd step count, mask value not 0/1, ...) */
+	LBM_ERR_CUDA = 2,   /* CUDA runtime/driver error, text in lbm_last_error() */
+	LBM_ERR_STATE = 3,  /* call order (e.g. run before upload/initialize) */
+	LBM_ERR_IO = 4      /* PrintLattice could not open its file */
+};
+
+enum { LBM_BUF_A = 0, LBM_BUF_B = 1 };
+
+/* The compile-time constants of LB.c:46-56, as run-time fields. */
+typedef struct {
+	int nx, ny;        /* NX, NY (LB.c:46-47): global rows (x, slow) / columns (y, contiguous) */
+	real_t tau;        /* TAU (LB.c:48) */
+	real_t accel;      /* ACCEL (LB.c:55) */
+	int vecwidth;      /* VECWIDTH of the reference build being matched (prec_*.h):
+	                      4/2/1 DP, 8/4/1 SP; 0 = the prec_*_cuda.h default (AVX).
+	                      1 selects the rounding order of StreamCollide (LB.c:216-302)
+	                      everywhere, >1 that of StreamCollideVec (LB.c:307-484) for
+	                      j < NYVECMAX and of StreamCollide for the tail columns. */
+	int device;        /* CUDA device ordinal */
+	int row_lo, row_hi;/* this slab owns global rows [row_lo,row_hi); 0,0 = whole lattice.
+	                      The reference's MPI row-slab decomposition (README.md:44-53). */
+} lbm_config;
+
+/* Closed-form scenes.  lbm_scene_reference() is InitializeArrays (LB.c:551-606). */
+typedef struct {
+	real_t rho0;                 /* INITIALDENSITY (LB.c:56): fA = rho0*omega_s at rest, fB = 0 */
+	int channel_walls;           /* rows 0 and nx-1 solid (LB.c:575-578) */
+	int bar_i0, bar_i1, bar_j0, bar_j1; /* solid box rows [i0,i1) x cols [j0,j1) (LB.c:567-573); empty if i0>=i1 */
+	long long disc_ci, disc_cj, disc_r; /* solid disc (i-ci)^2+(j-cj)^2 <= r^2 in integers; r<0: none */
+} lbm_scene;
+
+int lbm_sizeof_real(void);            /* 8 (dp library) or 4 (sp library) */
+const char *lbm_last_error(void);     /* text of the last failure on this thread */
+const char *lbm_version(void);
+
+/* ---- lifetime (replaces the _mm_malloc/_mm_free block LB.c:136-140,177-179) ---- */
+int lbm_create(lbm_ctx **out, const lbm_config *cfg);
+int lbm_destroy(lbm_ctx *ctx);
+
+/* ---- inputs ---- */
+/* InitializeArrays (LB.c:551-606), evaluated on the device for the rows this slab owns. */
+lbm_scene lbm_scene_reference(void);
+int lbm_initialize_arrays(lbm_ctx *ctx, const lbm_scene *scene);
+/* Host arrays in the reference layout, covering the GLOBAL lattice (nx rows); the slab
+ * takes its own rows.  fB may be NULL (zeros, LB.c:593-601).  walls values must be 0/1. */
+int lbm_upload(lbm_ctx *ctx, const real_t *fA, const real_t *fB, const char *walls, int ldy);
+/* Copies this slab's rows into global-layout host arrays; either pointer may be NULL.
+ * walls_out (optional) receives the unpacked device bitmask as chars. */
+int lbm_download(lbm_ctx *ctx, real_t *fA, real_t *fB, char *walls_out, int ldy);
+
+/* ---- the timestep path ---- */
+/* DoTimeStep (LB.c:186-210): Source(A); A->B; Source(B); B->A.  Asynchronous. */
+int lbm_do_timestep(lbm_ctx *ctx);
+/* The loop LB.c:148-164 without the prints: nsteps (even) lattice steps.  Asynchronous. */
+int lbm_run(lbm_ctx *ctx, int nsteps);
+/* Same, bracketed by CUDA events on the context's stream; *ms = device time. Synchronous. */
+int lbm_run_timed(lbm_ctx *ctx, int nsteps, float *ms);
+/* ApplySource (LB.c:489-518) on device buffer `buf`, in place. */
+int lbm_apply_source(lbm_ctx *ctx, int buf);
+/* StreamCollideVec + StreamCollide tail (LB.c:195-196 / 204-205): one pull step
+ * src_buf -> the other buffer, no source term. */
+int lbm_stream_collide(lbm_ctx *ctx, int src_buf);
+int lbm_sync(lbm_ctx *ctx);
+
+/* ---- observers ---- */
+/* ComputeReynolds (LB.c:522-547) on buffer A: the centre column is gathered on the
+ * device, summed on the host in the reference's serial order.  `column`/`valid`
+ * variant below is for slab runs: each slab contributes its rows. */
+int lbm_compute_reynolds(lbm_ctx *ctx, real_t *re);
+/* u_y of the centre column for this slab's rows (uy[nx_local]) and the fluid flags
+ * (LB.c:533-540); a multi-slab caller concatenates them in row order and finishes with
+ * lbm_reynolds_from_column. */
+int lbm_reynolds_column(lbm_ctx *ctx, real_t *uy, char *is_fluid);
+real_t lbm_reynolds_from_column(const real_t *uy, const char *is_fluid, int nx, real_t tau);
+/* rho, u_x, u_y of every site of buffer A in the order of PrintLattice (LB.c:621-629);
+ * outputs are dense [nx_local][ny]; any may be NULL. */
+int lbm_macroscopic(lbm_ctx *ctx, real_t *rho, real_t *ux, real_t *uy);
+/* PrintLattice (LB.c:610-639): CSV of u_x^2+u_y^2, "%.10lf", ", " separated, one lattice
+ * row per line.  `path` replaces the hard-wired data/<timeStep>.csv. */
+int lbm_print_lattice(lbm_ctx *ctx, const char *path);
+
+/* ---- slab decomposition / halo exchange (README.md:44-53; no reference source) ---- */
+typedef struct {
+	int nx_local, ny, row_lo, row_hi;
+	size_t ldy;            /* device row stride in elements */
+	size_t plane;          /* device plane stride in elements = (nx_local+2)*ldy */
+	size_t halo_bytes;     /* bytes of one packed halo message: 3*ny*sizeof(real_t) */
+	void *dev_f[2];        /* device base of buffers A, B (row 0 = lower halo row) */
+	void *dev_flags;       /* device int[4]: neighbour-barrier slots */
+} lbm_slab_info;
+int lbm_slab_info_get(lbm_ctx *ctx, lbm_slab_info *info);
+
+/* 64-byte CUDA IPC handles for fA, fB and the flag words, to be shipped to the ring
+ * neighbours by the caller (torch.distributed / MPI / a pipe). */
+#define LBM_IPC_BLOB_BYTES 256
+int lbm_ipc_export(lbm_ctx *ctx, unsigned char blob[LBM_IPC_BLOB_BYTES]);
+/* Connect the ring: `up` owns rows starting at row_hi, `dn` owns rows ending at row_lo
+ * (both wrap periodically, LB.c:231-232).  After this call the boundary-row kernels store
+ * their halo speeds (2,5,6 upwards; 4,7,8 downwards; LB.c:237-243) straight into the
+ * neighbour's halo rows over NVLink, and steps are ordered by device-side flags. */
+int lbm_ipc_connect(lbm_ctx *ctx, const unsigned char up[LBM_IPC_BLOB_BYTES],
+                    const unsigned char dn[LBM_IPC_BLOB_BYTES]);
+/* Same wiring for slabs living in ONE process (several GPUs with peer access, or several
+ * logical slabs on one GPU for decomposition-invariance tests).  Ordering between slabs is
+ * then the caller's: use lbm_group_run. */
+int lbm_connect_local(lbm_ctx *ctx, lbm_ctx *up, lbm_ctx *dn);
+/* Steps a ring of in-process slabs together (slabs[k] owns the k-th row range). */
+int lbm_group_run(lbm_ctx **slabs, int nslabs, int nsteps);
+
+/* Staged exchange for a transport the caller owns (NCCL send/recv through
+ * torch.distributed): pack this slab's boundary rows of `buf` into two contiguous device
+ * messages, and unpack two received messages into the halo rows of `buf`. */
+int lbm_halo_pack(lbm_ctx *ctx, int buf, void *dev_to_up, void *dev_to_dn);
+int lbm_halo_unpack(lbm_ctx *ctx, int buf, const void *dev_from_dn, const void *dev_from_up);
+/* One lattice step src_buf -> other restricted to local rows [r0,r1), used by a caller that
+ * overlaps its own exchange with inner-row compute.  stream_id 0 = main, 1 = boundary. */
+int lbm_step_rows(lbm_ctx *ctx, int src_buf, int r0, int r1, int tail_source, int stream_id);
+int lbm_stream_handle(lbm_ctx *ctx, int stream_id, void **cuda_stream);
+int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary stream and vice versa */
+
+/* ---- tuning / accounting ---- */
+typedef struct {
+	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = default */
+	int block;        /* threads per CTA; 0 = default */
+	int neighbour;    /* 0 = warp shuffle for the +-1 column element, 1 = direct load, 2 = TMA-staged rows */
+	int hints;        /* 0 = default caching, 1 = L1::no_allocate loads + .cs stores */
+	int ctas_per_sm;  /* >0: persistent grid of 148*ctas_per_sm CTAs, 0 = one pass */
+	int use_graph;    /* replay steps from a captured CUDA graph */
+} lbm_tuning;
+int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
+int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
+/* Kernels launched by this context since creation (bench.py's gpu_launches). */
+long long lbm_kernel_launches(lbm_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LBM_B200_H */

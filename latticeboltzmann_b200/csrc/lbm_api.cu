@@ -1,0 +1,878 @@
+// lbm_api.cu -- the C ABI declared in include/lbm_b200.h (host side, thin).
+//
+// Compiled twice: -DLBM_DOUBLE -> liblbm_b200_dp.so, -DLBM_FLOAT -> liblbm_b200_sp.so
+// (the reference chooses precision the same way, by header, LB.c:59-65).
+// No CPU fallback anywhere: without a usable sm_100 device every call fails.
+#if defined(LBM_DOUBLE)
+#include "prec_double_cuda.h"
+#elif defined(LBM_FLOAT)
+#include "prec_float_cuda.h"
+#else
+#error "compile with -DLBM_DOUBLE or -DLBM_FLOAT"
+#endif
+#include "lbm_b200.h"
+#include "lbm_kernels.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+using namespace lbm;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof g_err, fmt, ap);
+	va_end(ap);
+	return code;
+}
+
+#define CK(call)                                                                                   \
+	do {                                                                                           \
+		cudaError_t e_ = (call);                                                                   \
+		if (e_ != cudaSuccess)                                                                     \
+			return fail(LBM_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+	} while (0)
+
+enum { SYNC_SELF = 0, SYNC_LOCAL = 1, SYNC_FLAGS = 2 };
+
+struct Peer {
+	real_t *f[2];      // neighbour's buffers A, B (storage row 0)
+	int *flags;        // neighbour's flag words
+	int nxl;           // neighbour's owned rows
+};
+
+struct IpcBlob {           // what lbm_ipc_export ships (<= LBM_IPC_BLOB_BYTES)
+	char magic[8];
+	cudaIpcMemHandle_t f[2];
+	cudaIpcMemHandle_t flags;
+	int nxl, ny, device, pid;
+	unsigned long long uid;
+};
+static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "blob too large");
+
+} // namespace
+
+struct lbm_ctx {
+	lbm_config cfg;
+	int nxl, ny, vw, nyvec, ldy, ldw;
+	size_t plane;
+	real_t *f[2];
+	uint32_t *mask;
+	int *flags;                  // device int[4]: [0] from dn, [1] from up, [3] timeout
+	cudaStream_t stream[2];      // 0 main (inner rows), 1 boundary rows
+	cudaEvent_t ev_main, ev_bnd[2], ev_t0, ev_t1;
+	Peer up, dn;
+	int sync_mode;
+	int epoch;
+	void *ipc_opened[6];
+	int n_ipc_opened;
+	lbm_tuning tune;
+	long long launches;
+	int has_state;
+	real_t w0, w14, w58, itau, a14, a58;
+	double itau_d;
+	// captured CUDA graph of one DoTimeStep-pair in steady state
+	cudaGraphExec_t graph_exec;
+	int graph_steps;
+};
+
+namespace {
+
+int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_OK; }
+
+StepParams<real_t> make_params(const lbm_ctx *c, int src, int r0, int r1, int tail_source)
+{
+	StepParams<real_t> p;
+	const int dst = src ^ 1;
+	p.src = c->f[src];
+	p.dst = c->f[dst];
+	p.mask = c->mask;
+	p.plane = c->plane;
+	p.up_plane = (size_t)(c->up.nxl + 2) * c->ldy;
+	p.dn_plane = (size_t)(c->dn.nxl + 2) * c->ldy;
+	p.up_halo = c->up.f[dst];                                          // neighbour's storage row 0
+	p.dn_halo = c->dn.f[dst] + (size_t)(c->dn.nxl + 1) * c->ldy;       // neighbour's storage row nxl'+1
+	p.ldy = c->ldy; p.ldw = c->ldw;
+	p.nxl = c->nxl; p.ny = c->ny;
+	p.jmin = 0; p.jmax = c->nyvec;
+	p.r0 = r0; p.r1 = r1;
+	p.vw = c->vw;
+	p.tail_source = tail_source;
+	p.w0 = c->w0; p.w14 = c->w14; p.w58 = c->w58;
+	p.itau = c->itau; p.itau_d = c->itau_d;
+	p.a14 = c->a14; p.a58 = c->a58;
+	return p;
+}
+
+} // namespace
+
+extern "C" {
+
+int lbm_sizeof_real(void) { return (int)sizeof(real_t); }
+const char *lbm_last_error(void) { return g_err; }
+const char *lbm_version(void) { return "latticeboltzmann_b200 0.1 (" LBM_PREC_TAG ", sm_100a)"; }
+
+lbm_scene lbm_scene_reference(void)
+{
+	lbm_scene s;
+	s.rho0 = REAL_T(0.1);                 /* LB.c:56 */
+	s.channel_walls = 1;                  /* LB.c:575-578 */
+	s.bar_i0 = 20; s.bar_i1 = 220;        /* LB.c:567 */
+	s.bar_j0 = 100; s.bar_j1 = 105;       /* LB.c:568-572 */
+	s.disc_ci = s.disc_cj = 0; s.disc_r = -1;
+	return s;
+}
+
+int lbm_create(lbm_ctx **out, const lbm_config *cfg)
+{
+	if (!out || !cfg) return fail(LBM_ERR_ARG, "lbm_create: null argument");
+	*out = nullptr;
+	if (cfg->nx < 1 || cfg->ny < 2) return fail(LBM_ERR_ARG, "lbm_create: lattice %dx%d too small", cfg->nx, cfg->ny);
+	int vw = cfg->vecwidth ? cfg->vecwidth : VECWIDTH;
+	if (vw != 1 && vw != 2 && vw != 4 && vw != 8) return fail(LBM_ERR_ARG, "lbm_create: vecwidth %d not in {1,2,4,8}", vw);
+	int lo = cfg->row_lo, hi = cfg->row_hi;
+	if (lo == 0 && hi == 0) hi = cfg->nx;
+	if (lo < 0 || hi > cfg->nx || lo >= hi) return fail(LBM_ERR_ARG, "lbm_create: bad slab rows [%d,%d) of %d", lo, hi, cfg->nx);
+
+	int ndev = 0;
+	CK(cudaGetDeviceCount(&ndev));
+	if (cfg->device < 0 || cfg->device >= ndev) return fail(LBM_ERR_CUDA, "lbm_create: device %d of %d", cfg->device, ndev);
+	CK(cudaSetDevice(cfg->device));
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, cfg->device));
+	if (prop.major != 10) return fail(LBM_ERR_CUDA, "lbm_create: device is sm_%d%d, this library carries sm_100a code only", prop.major, prop.minor);
+
+	lbm_ctx *c = new lbm_ctx();
+	memset(c, 0, sizeof *c);
+	c->cfg = *cfg;
+	c->cfg.row_lo = lo; c->cfg.row_hi = hi; c->cfg.vecwidth = vw;
+	c->nxl = hi - lo;
+	c->ny = cfg->ny;
+	c->vw = vw;
+	c->nyvec = vw * (cfg->ny / vw);                           /* NYVECMAX, LB.c:76 */
+	const int per128 = 128 / (int)sizeof(real_t);
+	c->ldy = ((cfg->ny + per128 - 1) / per128) * per128;      /* rows padded to 128 B */
+	c->ldw = (((cfg->ny + 31) / 32) + 3) / 4 * 4;
+	c->plane = (size_t)(c->nxl + 2) * c->ldy;
+	if ((unsigned long long)c->nxl * (unsigned long long)c->ny >= 0xffffffffull) {
+		delete c;
+		return fail(LBM_ERR_ARG, "lbm_create: slab has >= 2^32 sites");
+	}
+
+	/* constants formed in real_t exactly as the reference's literals are (LB.c:38-40,323,502) */
+	c->w0 = REAL_T(4.0) / REAL_T(9.0);
+	c->w14 = REAL_T(1.0) / REAL_T(9.0);
+	c->w58 = REAL_T(1.0) / REAL_T(36.0);
+	c->itau = REAL_T(1.0) / cfg->tau;
+	c->itau_d = 1.0 / (double)cfg->tau;
+	c->a14 = cfg->accel * c->w14;
+	c->a58 = cfg->accel * c->w58;
+
+	const size_t fbytes = 9 * c->plane * sizeof(real_t);
+	cudaError_t e = cudaMalloc(&c->f[0], fbytes);
+	if (e == cudaSuccess) e = cudaMalloc(&c->f[1], fbytes);
+	if (e == cudaSuccess) e = cudaMalloc(&c->mask, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
+	if (e == cudaSuccess) e = cudaMalloc(&c->flags, 4 * sizeof(int));
+	if (e == cudaSuccess) e = cudaMemset(c->f[0], 0, fbytes);
+	if (e == cudaSuccess) e = cudaMemset(c->f[1], 0, fbytes);
+	if (e == cudaSuccess) e = cudaMemset(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
+	if (e == cudaSuccess) e = cudaMemset(c->flags, 0, 4 * sizeof(int));
+	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaStreamCreateWithFlags(&c->stream[k], cudaStreamNonBlocking);
+	if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming);
+	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&c->ev_bnd[k], cudaEventDisableTiming);
+	if (e == cudaSuccess) e = cudaEventCreate(&c->ev_t0);
+	if (e == cudaSuccess) e = cudaEventCreate(&c->ev_t1);
+	if (e != cudaSuccess) {
+		fail(LBM_ERR_CUDA, "lbm_create: %s (%.2f GB requested)", cudaGetErrorString(e), 2.0 * fbytes / 1e9);
+		lbm_destroy(c);
+		return LBM_ERR_CUDA;
+	}
+	/* P == 1: the slab is its own ring neighbour (x wraps periodically, LB.c:231-232) */
+	c->up.f[0] = c->dn.f[0] = c->f[0];
+	c->up.f[1] = c->dn.f[1] = c->f[1];
+	c->up.flags = c->dn.flags = c->flags;
+	c->up.nxl = c->dn.nxl = c->nxl;
+	c->sync_mode = SYNC_SELF;
+
+	c->tune.vec = sizeof(real_t) == 8 ? 2 : 4;
+	c->tune.block = 256;
+	c->tune.neighbour = 0;
+	c->tune.hints = 0;
+	c->tune.ctas_per_sm = 0;
+	c->tune.use_graph = 0;
+	*out = c;
+	return LBM_OK;
+}
+
+int lbm_destroy(lbm_ctx *c)
+{
+	if (!c) return LBM_OK;
+	cudaSetDevice(c->cfg.device);
+	cudaDeviceSynchronize();
+	if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
+	for (int k = 0; k < c->n_ipc_opened; k++) cudaIpcCloseMemHandle(c->ipc_opened[k]);
+	for (int k = 0; k < 2; k++) {
+		if (c->f[k]) cudaFree(c->f[k]);
+		if (c->stream[k]) cudaStreamDestroy(c->stream[k]);
+		if (c->ev_bnd[k]) cudaEventDestroy(c->ev_bnd[k]);
+	}
+	if (c->mask) cudaFree(c->mask);
+	if (c->flags) cudaFree(c->flags);
+	if (c->ev_main) cudaEventDestroy(c->ev_main);
+	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
+	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+	delete c;
+	return LBM_OK;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------
+// step launch
+// ---------------------------------------------------------------------------
+namespace {
+
+template <int V, int NB, int HINT>
+cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st)
+{
+	stream_collide_vec_kernel<real_t, V, NB, HINT><<<grid, block, 0, st>>>(p);
+	return cudaGetLastError();
+}
+
+template <int V>
+cudaError_t launch_vec_v(int nb, int hint, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st)
+{
+	if (nb == 0 && hint == 0) return launch_vec_inst<V, 0, 0>(p, grid, block, st);
+	if (nb == 0 && hint == 1) return launch_vec_inst<V, 0, 1>(p, grid, block, st);
+	if (nb == 1 && hint == 0) return launch_vec_inst<V, 1, 0>(p, grid, block, st);
+	return launch_vec_inst<V, 1, 1>(p, grid, block, st);
+}
+
+int sm_count(int device)
+{
+	static int cached[64] = {0};
+	if (device < 64 && cached[device]) return cached[device];
+	int n = 148;
+	cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+	if (device < 64) cached[device] = n;
+	return n;
+}
+
+// One pull step src -> src^1 over owned rows [r0,r1): vector kernel for j < NYVECMAX,
+// scalar-order kernel for the ragged tail (LB.c:195-196) or for everything (LB.c:198).
+int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st)
+{
+	if (r1 <= r0) return LBM_OK;
+	StepParams<real_t> p = make_params(c, src, r0, r1, tail_source);
+	const unsigned rows = (unsigned)(r1 - r0);
+	int jtail = 0;
+	if (c->vw > 1 && c->nyvec > 0) {
+		int V = c->tune.vec;
+		if (V > c->vw) V = c->vw;
+		const unsigned block = (unsigned)c->tune.block;
+		const unsigned long long total = (unsigned long long)rows * (unsigned)(c->nyvec / V);
+		unsigned long long grid = (total + block - 1) / block;
+		if (c->tune.ctas_per_sm > 0) {
+			const unsigned long long cap = (unsigned long long)sm_count(c->cfg.device) * c->tune.ctas_per_sm;
+			if (grid > cap) grid = cap;
+		}
+		cudaError_t e;
+		switch (V) {
+		case 1: e = launch_vec_v<1>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
+		case 2: e = launch_vec_v<2>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
+		case 4: e = launch_vec_v<4>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
+#ifdef LBM_FLOAT
+		case 8: e = launch_vec_v<8>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
+#endif
+		default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
+		}
+		if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_vec_kernel: %s", cudaGetErrorString(e));
+		c->launches++;
+		jtail = c->nyvec;
+	}
+	if (jtail < c->ny) {
+		p.jmin = jtail; p.jmax = c->ny;
+		const unsigned long long total = (unsigned long long)rows * (unsigned)(c->ny - jtail);
+		const unsigned block = 256;
+		unsigned long long grid = (total + block - 1) / block;
+		const unsigned long long cap = (unsigned long long)sm_count(c->cfg.device) * 16;
+		if (grid > cap) grid = cap;
+		stream_collide_scalar_kernel<real_t><<<(unsigned)grid, block, 0, st>>>(p);
+		cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_scalar_kernel: %s", cudaGetErrorString(e));
+		c->launches++;
+	}
+	return LBM_OK;
+}
+
+int launch_source(lbm_ctx *c, int buf, cudaStream_t st)
+{
+	StepParams<real_t> p = make_params(c, buf, 0, c->nxl, 0);
+	apply_source_kernel<real_t><<<(c->nxl + 127) / 128, 128, 0, st>>>(c->f[buf], p);
+	CK(cudaGetLastError());
+	c->launches++;
+	return LBM_OK;
+}
+
+// refresh the neighbours' (or, P == 1, our own) halo rows of buffer `buf` from our boundary rows
+int launch_halo_push(lbm_ctx *c, int buf, cudaStream_t st)
+{
+	StepParams<real_t> p = make_params(c, buf ^ 1, 0, c->nxl, 0);   // "dst" == buf
+	halo_push_kernel<real_t><<<(c->ny + 255) / 256, 256, 0, st>>>(c->f[buf], p);
+	CK(cudaGetLastError());
+	c->launches++;
+	return LBM_OK;
+}
+
+// neighbour barrier through device flags (ranks in other processes): announce, then wait
+int launch_signal(lbm_ctx *c, cudaStream_t st)
+{
+	c->epoch++;
+	flag_signal_kernel<<<1, 1, 0, st>>>(c->up.flags + 0, c->dn.flags + 1, c->epoch);
+	CK(cudaGetLastError());
+	c->launches++;
+	return LBM_OK;
+}
+int launch_wait(lbm_ctx *c, cudaStream_t st)
+{
+	flag_wait_kernel<<<1, 1, 0, st>>>(c->flags, c->epoch, 20ull * 1000 * 1000 * 1000);
+	CK(cudaGetLastError());
+	c->launches++;
+	return LBM_OK;
+}
+
+// One lattice step of this slab, with the neighbour ordering its sync mode needs.
+//   SYNC_SELF : single launch over all rows (halo push lands in our own halo rows).
+//   SYNC_FLAGS: boundary rows first on stream 1 (wait for the neighbours' previous step,
+//               compute rows 0 and nxl-1 storing their halos into the neighbours over NVLink,
+//               announce), inner rows meanwhile on stream 0, then join -- the reference's
+//               "hide the exchange behind the inner rows" (README.md:45-51).
+//   SYNC_LOCAL: like SYNC_FLAGS but ordered by the caller (lbm_group_run) with events.
+int enqueue_step(lbm_ctx *c, int src, int tail_source)
+{
+	int rc;
+	if (c->sync_mode == SYNC_SELF) return launch_step(c, src, 0, c->nxl, tail_source, c->stream[0]);
+	if (c->sync_mode == SYNC_FLAGS) {
+		CK(cudaEventRecord(c->ev_main, c->stream[0]));
+		CK(cudaStreamWaitEvent(c->stream[1], c->ev_main, 0));
+		if ((rc = launch_wait(c, c->stream[1]))) return rc;
+		if ((rc = launch_step(c, src, 0, 1, tail_source, c->stream[1]))) return rc;
+		if (c->nxl > 1 && (rc = launch_step(c, src, c->nxl - 1, c->nxl, tail_source, c->stream[1]))) return rc;
+		if ((rc = launch_signal(c, c->stream[1]))) return rc;
+		CK(cudaEventRecord(c->ev_bnd[0], c->stream[1]));
+		if ((rc = launch_step(c, src, 1, c->nxl - 1, tail_source, c->stream[0]))) return rc;
+		CK(cudaStreamWaitEvent(c->stream[0], c->ev_bnd[0], 0));
+		return LBM_OK;
+	}
+	return fail(LBM_ERR_STATE, "slab is wired with lbm_connect_local: step it through lbm_group_run");
+}
+
+// ApplySource + halo refresh + neighbour barrier that open every run (the first step's source
+// cannot be fused into a previous kernel's tail)
+int enqueue_prologue(lbm_ctx *c, int buf)
+{
+	int rc;
+	if ((rc = launch_source(c, buf, c->stream[0]))) return rc;
+	if ((rc = launch_halo_push(c, buf, c->stream[0]))) return rc;
+	if (c->sync_mode == SYNC_FLAGS && (rc = launch_signal(c, c->stream[0]))) return rc;
+	return LBM_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------------------
+// inputs
+// ---------------------------------------------------------------------------
+int lbm_initialize_arrays(lbm_ctx *c, const lbm_scene *scene)
+{
+	if (!c || !scene) return fail(LBM_ERR_ARG, "lbm_initialize_arrays: null argument");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	SceneDev sc;
+	sc.nx = c->cfg.nx;
+	sc.channel_walls = scene->channel_walls;
+	sc.bar_i0 = scene->bar_i0; sc.bar_i1 = scene->bar_i1; sc.bar_j0 = scene->bar_j0; sc.bar_j1 = scene->bar_j1;
+	sc.disc_ci = scene->disc_ci; sc.disc_cj = scene->disc_cj;
+	sc.disc_r2 = scene->disc_r < 0 ? -1 : scene->disc_r * scene->disc_r;
+	cudaStream_t st = c->stream[0];
+	const size_t nwords = (size_t)c->nxl * c->ldw, nsites = (size_t)c->nxl * c->ny;
+	scene_mask_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(c->mask, sc, c->cfg.row_lo, c->nxl, c->ny, c->ldw);
+	CK(cudaGetLastError());
+	/* INITIALDENSITY * OMEGA_s in real_t (LB.c:583-591) */
+	scene_fill_kernel<real_t><<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(
+		c->f[0], c->f[1], c->plane, c->ldy, c->nxl, c->ny, scene->rho0 * c->w0, scene->rho0 * c->w14, scene->rho0 * c->w58);
+	CK(cudaGetLastError());
+	c->launches += 2;
+	c->has_state = 1;
+	return LBM_OK;
+}
+
+int lbm_upload(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *walls, int ldy)
+{
+	if (!c || !fA || !walls) return fail(LBM_ERR_ARG, "lbm_upload: null argument");
+	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_upload: ldy %d < ny %d", ldy, c->ny);
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	cudaStream_t st = c->stream[0];
+	const size_t hplane = (size_t)c->cfg.nx * ldy;              /* host plane stride, I() of LB.c:72 */
+	const size_t row0 = (size_t)c->cfg.row_lo * ldy;
+	for (int b = 0; b < 2; b++) {
+		const real_t *src = b == 0 ? fA : fB;
+		if (!src) {                                              /* fB = 0 (LB.c:593-601) */
+			CK(cudaMemsetAsync(c->f[1], 0, 9 * c->plane * sizeof(real_t), st));
+			continue;
+		}
+		for (int s = 0; s < 9; s++)
+			CK(cudaMemcpy2DAsync(c->f[b] + s * c->plane + c->ldy, (size_t)c->ldy * sizeof(real_t),
+			                     src + s * hplane + row0, (size_t)ldy * sizeof(real_t),
+			                     (size_t)c->ny * sizeof(real_t), (size_t)c->nxl, cudaMemcpyHostToDevice, st));
+	}
+	/* walls: chars -> device scratch -> packed bits */
+	char *dwalls = nullptr;
+	int *dbad = nullptr;
+	const size_t ldc = (size_t)c->ny;
+	CK(cudaMallocAsync(&dwalls, (size_t)c->nxl * ldc, st));
+	CK(cudaMallocAsync(&dbad, sizeof(int), st));
+	CK(cudaMemsetAsync(dbad, 0, sizeof(int), st));
+	CK(cudaMemcpy2DAsync(dwalls, ldc, walls + row0, (size_t)ldy, (size_t)c->ny, (size_t)c->nxl, cudaMemcpyHostToDevice, st));
+	const size_t nwords = (size_t)c->nxl * c->ldw;
+	mask_pack_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(dwalls, ldc, c->mask, c->nxl, c->ny, c->ldw, dbad);
+	CK(cudaGetLastError());
+	c->launches++;
+	int bad = 0;
+	CK(cudaMemcpyAsync(&bad, dbad, sizeof(int), cudaMemcpyDeviceToHost, st));
+	CK(cudaFreeAsync(dwalls, st));
+	CK(cudaFreeAsync(dbad, st));
+	CK(cudaStreamSynchronize(st));
+	if (bad) return fail(LBM_ERR_ARG, "lbm_upload: walls must hold 0 or 1 (LB.c:246 tests == 1, LB.c:455 tests == 0)");
+	c->has_state = 1;
+	return LBM_OK;
+}
+
+int lbm_download(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_download: null ctx");
+	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_download: ldy %d < ny %d", ldy, c->ny);
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	cudaStream_t st = c->stream[0];
+	const size_t hplane = (size_t)c->cfg.nx * ldy, row0 = (size_t)c->cfg.row_lo * ldy;
+	for (int b = 0; b < 2; b++) {
+		real_t *dst = b == 0 ? fA : fB;
+		if (!dst) continue;
+		for (int s = 0; s < 9; s++)
+			CK(cudaMemcpy2DAsync(dst + s * hplane + row0, (size_t)ldy * sizeof(real_t),
+			                     c->f[b] + s * c->plane + c->ldy, (size_t)c->ldy * sizeof(real_t),
+			                     (size_t)c->ny * sizeof(real_t), (size_t)c->nxl, cudaMemcpyDeviceToHost, st));
+	}
+	if (walls_out) {
+		char *dwalls = nullptr;
+		const size_t ldc = (size_t)c->ny, nsites = (size_t)c->nxl * c->ny;
+		CK(cudaMallocAsync(&dwalls, nsites, st));
+		mask_unpack_kernel<<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(c->mask, dwalls, ldc, c->nxl, c->ny, c->ldw);
+		CK(cudaGetLastError());
+		c->launches++;
+		CK(cudaMemcpy2DAsync(walls_out + row0, (size_t)ldy, dwalls, ldc, (size_t)c->ny, (size_t)c->nxl, cudaMemcpyDeviceToHost, st));
+		CK(cudaFreeAsync(dwalls, st));
+	}
+	CK(cudaStreamSynchronize(st));
+	return LBM_OK;
+}
+
+// ---------------------------------------------------------------------------
+// the timestep path
+// ---------------------------------------------------------------------------
+int lbm_sync(lbm_ctx *c)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_sync: null ctx");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	CK(cudaStreamSynchronize(c->stream[1]));
+	CK(cudaStreamSynchronize(c->stream[0]));
+	if (c->sync_mode == SYNC_FLAGS) {
+		int fl[4];
+		CK(cudaMemcpy(fl, c->flags, sizeof fl, cudaMemcpyDeviceToHost));
+		if (fl[3]) return fail(LBM_ERR_STATE, "neighbour barrier timed out (a ring neighbour stopped stepping)");
+	}
+	return LBM_OK;
+}
+
+int lbm_run(lbm_ctx *c, int nsteps)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_run: null ctx");
+	if (nsteps < 0 || (nsteps & 1)) return fail(LBM_ERR_ARG, "lbm_run: nsteps %d must be even (LB.c:148 advances by 2)", nsteps);
+	if (!c->has_state) return fail(LBM_ERR_STATE, "lbm_run: no lattice loaded (lbm_upload / lbm_initialize_arrays first)");
+	if (nsteps == 0) return LBM_OK;
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	/* Source(A) of the first step; every later Source is fused into the tail of the step
+	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
+	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
+	for (int t = 0; t < nsteps; t++)
+		if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
+	return LBM_OK;
+}
+
+int lbm_do_timestep(lbm_ctx *c) { return lbm_run(c, 2); }
+
+int lbm_run_timed(lbm_ctx *c, int nsteps, float *ms)
+{
+	if (!c || !ms) return fail(LBM_ERR_ARG, "lbm_run_timed: null argument");
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	CK(cudaEventRecord(c->ev_t0, c->stream[0]));
+	if ((rc = lbm_run(c, nsteps))) return rc;
+	CK(cudaEventRecord(c->ev_t1, c->stream[0]));
+	if ((rc = lbm_sync(c))) return rc;
+	CK(cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
+	return LBM_OK;
+}
+
+int lbm_apply_source(lbm_ctx *c, int buf)
+{
+	if (!c || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_apply_source: bad argument");
+	if (c->sync_mode != SYNC_SELF) return fail(LBM_ERR_STATE, "lbm_apply_source: single-slab contexts only (use lbm_run)");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	if ((rc = launch_source(c, buf, c->stream[0]))) return rc;
+	return launch_halo_push(c, buf, c->stream[0]);
+}
+
+int lbm_stream_collide(lbm_ctx *c, int src_buf)
+{
+	if (!c || (src_buf != 0 && src_buf != 1)) return fail(LBM_ERR_ARG, "lbm_stream_collide: bad argument");
+	if (c->sync_mode != SYNC_SELF) return fail(LBM_ERR_STATE, "lbm_stream_collide: single-slab contexts only (use lbm_run)");
+	if (!c->has_state) return fail(LBM_ERR_STATE, "lbm_stream_collide: no lattice loaded");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	/* the source buffer may have been written by upload/apply_source: make its halo rows current */
+	if ((rc = launch_halo_push(c, src_buf, c->stream[0]))) return rc;
+	return launch_step(c, src_buf, 0, c->nxl, 0, c->stream[0]);
+}
+
+} // extern "C"
+
+extern "C" {
+
+// ---------------------------------------------------------------------------
+// observers
+// ---------------------------------------------------------------------------
+int lbm_reynolds_column(lbm_ctx *c, real_t *uy, char *is_fluid)
+{
+	if (!c || !uy || !is_fluid) return fail(LBM_ERR_ARG, "lbm_reynolds_column: null argument");
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	cudaStream_t st = c->stream[0];
+	const int jc = (int)((real_t)c->ny / 2.0);                  /* LB.c:527 */
+	real_t *duy = nullptr;
+	CK(cudaMallocAsync(&duy, (size_t)c->nxl * sizeof(real_t), st));
+	macroscopic_kernel<real_t><<<(c->nxl + 127) / 128, 128, 0, st>>>(c->f[0], c->plane, c->ldy, c->nxl, jc, 1,
+	                                                                 (real_t *)nullptr, (real_t *)nullptr, duy);
+	CK(cudaGetLastError());
+	c->launches++;
+	CK(cudaMemcpyAsync(uy, duy, (size_t)c->nxl * sizeof(real_t), cudaMemcpyDeviceToHost, st));
+	std::vector<uint32_t> words((size_t)c->nxl);
+	CK(cudaMemcpy2DAsync(words.data(), sizeof(uint32_t), c->mask + (jc >> 5), (size_t)c->ldw * sizeof(uint32_t),
+	                     sizeof(uint32_t), (size_t)c->nxl, cudaMemcpyDeviceToHost, st));
+	CK(cudaFreeAsync(duy, st));
+	CK(cudaStreamSynchronize(st));
+	for (int r = 0; r < c->nxl; r++) is_fluid[r] = (char)(((words[r] >> (jc & 31)) & 1u) == 0u);
+	return LBM_OK;
+}
+
+/* the serial accumulation and the final scaling of ComputeReynolds, LB.c:529-546 */
+real_t lbm_reynolds_from_column(const real_t *uy, const char *is_fluid, int nx, real_t tau)
+{
+	real_t total = 0;
+	int points = 0;
+	for (int i = 0; i < nx; i++)
+		if (is_fluid[i]) { total += uy[i]; points++; }
+	const real_t viscosity = REAL_T(1.0) / REAL_T(3.0) * (tau - REAL_T(1.0) / REAL_T(2.0));
+	return total / (real_t)points * REAL_T(10.0) / viscosity;
+}
+
+int lbm_compute_reynolds(lbm_ctx *c, real_t *re)
+{
+	if (!c || !re) return fail(LBM_ERR_ARG, "lbm_compute_reynolds: null argument");
+	if (c->nxl != c->cfg.nx) return fail(LBM_ERR_STATE, "lbm_compute_reynolds: slab context; gather lbm_reynolds_column over the ring");
+	std::vector<real_t> uy((size_t)c->nxl);
+	std::vector<char> fl((size_t)c->nxl);
+	int rc;
+	if ((rc = lbm_reynolds_column(c, uy.data(), fl.data()))) return rc;
+	*re = lbm_reynolds_from_column(uy.data(), fl.data(), c->nxl, c->cfg.tau);
+	return LBM_OK;
+}
+
+int lbm_macroscopic(lbm_ctx *c, real_t *rho, real_t *ux, real_t *uy)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_macroscopic: null ctx");
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	cudaStream_t st = c->stream[0];
+	const size_t n = (size_t)c->nxl * c->ny;
+	real_t *d[3] = {nullptr, nullptr, nullptr};
+	real_t *h[3] = {rho, ux, uy};
+	for (int k = 0; k < 3; k++)
+		if (h[k]) CK(cudaMallocAsync(&d[k], n * sizeof(real_t), st));
+	macroscopic_kernel<real_t><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(c->f[0], c->plane, c->ldy, c->nxl, 0, c->ny, d[0], d[1], d[2]);
+	CK(cudaGetLastError());
+	c->launches++;
+	for (int k = 0; k < 3; k++)
+		if (h[k]) {
+			CK(cudaMemcpyAsync(h[k], d[k], n * sizeof(real_t), cudaMemcpyDeviceToHost, st));
+			CK(cudaFreeAsync(d[k], st));
+		}
+	CK(cudaStreamSynchronize(st));
+	return LBM_OK;
+}
+
+int lbm_print_lattice(lbm_ctx *c, const char *path)
+{
+	if (!c || !path) return fail(LBM_ERR_ARG, "lbm_print_lattice: null argument");
+	const size_t n = (size_t)c->nxl * c->ny;
+	std::vector<real_t> ux(n), uy(n);
+	int rc;
+	if ((rc = lbm_macroscopic(c, nullptr, ux.data(), uy.data()))) return rc;
+	FILE *fp = fopen(path, "w");
+	if (!fp) return fail(LBM_ERR_IO, "Error opening file %s", path);       /* LB.c:616 */
+	std::vector<char> line((size_t)c->ny * 24 + 8);
+	for (int i = 0; i < c->nxl; i++) {
+		size_t pos = 0;
+		for (int j = 0; j < c->ny; j++) {
+			const real_t a = ux[(size_t)i * c->ny + j], b = uy[(size_t)i * c->ny + j];
+			const real_t u2 = a * a + b * b;                                 /* LB.c:631, real_t arithmetic */
+			pos += (size_t)snprintf(&line[pos], 24, "%.10lf", (double)u2);   /* LB.c:633 */
+			if (j < c->ny - 1) { line[pos++] = ','; line[pos++] = ' '; }     /* LB.c:634 */
+		}
+		line[pos++] = '\n';
+		fwrite(line.data(), 1, pos, fp);
+	}
+	fclose(fp);
+	return LBM_OK;
+}
+
+// ---------------------------------------------------------------------------
+// tuning / accounting
+// ---------------------------------------------------------------------------
+int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
+{
+	if (!c || !t) return fail(LBM_ERR_ARG, "lbm_set_tuning: null argument");
+	lbm_tuning n = *t;
+	if (n.vec == 0) n.vec = sizeof(real_t) == 8 ? 2 : 4;
+	if (n.block == 0) n.block = 256;
+	const int vmax = 32 / (int)sizeof(real_t);
+	if ((n.vec != 1 && n.vec != 2 && n.vec != 4 && n.vec != 8) || n.vec > vmax) return fail(LBM_ERR_ARG, "lbm_set_tuning: vec %d", n.vec);
+	if (n.block < 32 || n.block > 512 || (n.block & 31)) return fail(LBM_ERR_ARG, "lbm_set_tuning: block %d", n.block);
+	if (n.neighbour < 0 || n.neighbour > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: neighbour %d", n.neighbour);
+	if (n.hints < 0 || n.hints > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
+	if (n.ctas_per_sm < 0 || n.ctas_per_sm > 32) return fail(LBM_ERR_ARG, "lbm_set_tuning: ctas_per_sm %d", n.ctas_per_sm);
+	c->tune = n;
+	return LBM_OK;
+}
+int lbm_get_tuning(lbm_ctx *c, lbm_tuning *t)
+{
+	if (!c || !t) return fail(LBM_ERR_ARG, "lbm_get_tuning: null argument");
+	*t = c->tune;
+	return LBM_OK;
+}
+long long lbm_kernel_launches(lbm_ctx *c) { return c ? c->launches : 0; }
+
+} // extern "C"
+
+extern "C" {
+
+// ---------------------------------------------------------------------------
+// slab decomposition / halo exchange
+// ---------------------------------------------------------------------------
+int lbm_slab_info_get(lbm_ctx *c, lbm_slab_info *info)
+{
+	if (!c || !info) return fail(LBM_ERR_ARG, "lbm_slab_info_get: null argument");
+	info->nx_local = c->nxl; info->ny = c->ny;
+	info->row_lo = c->cfg.row_lo; info->row_hi = c->cfg.row_hi;
+	info->ldy = (size_t)c->ldy; info->plane = c->plane;
+	info->halo_bytes = (size_t)3 * c->ny * sizeof(real_t);
+	info->dev_f[0] = c->f[0]; info->dev_f[1] = c->f[1];
+	info->dev_flags = c->flags;
+	return LBM_OK;
+}
+
+int lbm_ipc_export(lbm_ctx *c, unsigned char blob[LBM_IPC_BLOB_BYTES])
+{
+	if (!c || !blob) return fail(LBM_ERR_ARG, "lbm_ipc_export: null argument");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	IpcBlob b;
+	memset(&b, 0, sizeof b);
+	memcpy(b.magic, "LBMIPC1", 8);
+	CK(cudaIpcGetMemHandle(&b.f[0], c->f[0]));
+	CK(cudaIpcGetMemHandle(&b.f[1], c->f[1]));
+	CK(cudaIpcGetMemHandle(&b.flags, c->flags));
+	b.nxl = c->nxl; b.ny = c->ny; b.device = c->cfg.device;
+	b.uid = (unsigned long long)(uintptr_t)c->f[0] ^ ((unsigned long long)c->cfg.row_lo << 48);
+	memset(blob, 0, LBM_IPC_BLOB_BYTES);
+	memcpy(blob, &b, sizeof b);
+	return LBM_OK;
+}
+
+int lbm_ipc_connect(lbm_ctx *c, const unsigned char up[LBM_IPC_BLOB_BYTES], const unsigned char dn[LBM_IPC_BLOB_BYTES])
+{
+	if (!c || !up || !dn) return fail(LBM_ERR_ARG, "lbm_ipc_connect: null argument");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	IpcBlob b[2];
+	memcpy(&b[0], up, sizeof(IpcBlob));
+	memcpy(&b[1], dn, sizeof(IpcBlob));
+	Peer peer[2];
+	for (int k = 0; k < 2; k++) {
+		if (memcmp(b[k].magic, "LBMIPC1", 8)) return fail(LBM_ERR_ARG, "lbm_ipc_connect: bad blob");
+		if (b[k].ny != c->ny) return fail(LBM_ERR_ARG, "lbm_ipc_connect: neighbour ny %d != %d", b[k].ny, c->ny);
+		if (k == 1 && !memcmp(&b[0], &b[1], sizeof(IpcBlob))) { peer[1] = peer[0]; break; }   /* P == 2: one neighbour, both sides */
+		void *ptr[3];
+		const cudaIpcMemHandle_t *h[3] = {&b[k].f[0], &b[k].f[1], &b[k].flags};
+		for (int m = 0; m < 3; m++) {
+			CK(cudaIpcOpenMemHandle(&ptr[m], *h[m], cudaIpcMemLazyEnablePeerAccess));
+			c->ipc_opened[c->n_ipc_opened++] = ptr[m];
+		}
+		peer[k].f[0] = (real_t *)ptr[0]; peer[k].f[1] = (real_t *)ptr[1];
+		peer[k].flags = (int *)ptr[2];
+		peer[k].nxl = b[k].nxl;
+	}
+	c->up = peer[0];
+	c->dn = peer[1];
+	c->sync_mode = SYNC_FLAGS;
+	c->epoch = 0;
+	CK(cudaMemset(c->flags, 0, 4 * sizeof(int)));
+	return LBM_OK;
+}
+
+int lbm_connect_local(lbm_ctx *c, lbm_ctx *up, lbm_ctx *dn)
+{
+	if (!c || !up || !dn) return fail(LBM_ERR_ARG, "lbm_connect_local: null argument");
+	if (up->ny != c->ny || dn->ny != c->ny) return fail(LBM_ERR_ARG, "lbm_connect_local: ny mismatch");
+	lbm_ctx *nb[2] = {up, dn};
+	for (int k = 0; k < 2; k++) {
+		if (nb[k]->cfg.device != c->cfg.device) {
+			int can = 0;
+			CK(cudaDeviceCanAccessPeer(&can, c->cfg.device, nb[k]->cfg.device));
+			if (!can) return fail(LBM_ERR_CUDA, "lbm_connect_local: no peer access %d -> %d", c->cfg.device, nb[k]->cfg.device);
+			CK(cudaSetDevice(c->cfg.device));
+			cudaError_t e = cudaDeviceEnablePeerAccess(nb[k]->cfg.device, 0);
+			if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CK(e);
+			cudaGetLastError();
+		}
+	}
+	c->up.f[0] = up->f[0]; c->up.f[1] = up->f[1]; c->up.flags = up->flags; c->up.nxl = up->nxl;
+	c->dn.f[0] = dn->f[0]; c->dn.f[1] = dn->f[1]; c->dn.flags = dn->flags; c->dn.nxl = dn->nxl;
+	c->sync_mode = SYNC_LOCAL;
+	return LBM_OK;
+}
+
+/* All slabs of a ring that live in this process step together.  Per step and slab:
+ * boundary rows on stream 1 once the neighbours' previous boundary kernels are done
+ * (cross-device event waits), inner rows on stream 0 meanwhile, then join. */
+int lbm_group_run(lbm_ctx **slabs, int n, int nsteps)
+{
+	if (!slabs || n < 1) return fail(LBM_ERR_ARG, "lbm_group_run: bad argument");
+	if (nsteps < 0 || (nsteps & 1)) return fail(LBM_ERR_ARG, "lbm_group_run: nsteps %d must be even", nsteps);
+	if (nsteps == 0) return LBM_OK;
+	int rc;
+	for (int k = 0; k < n; k++) {
+		lbm_ctx *c = slabs[k];
+		if (!c->has_state) return fail(LBM_ERR_STATE, "lbm_group_run: slab %d has no lattice", k);
+		if (n > 1 && c->sync_mode != SYNC_LOCAL) return fail(LBM_ERR_STATE, "lbm_group_run: slab %d not wired (lbm_connect_local)", k);
+	}
+	if (n == 1) return lbm_run(slabs[0], nsteps);
+	/* prologue: Source(A) and halo refresh everywhere, recorded as "boundary of step -1" */
+	for (int k = 0; k < n; k++) {
+		lbm_ctx *c = slabs[k];
+		if ((rc = set_device(c))) return rc;
+		if ((rc = launch_source(c, LBM_BUF_A, c->stream[0]))) return rc;
+		if ((rc = launch_halo_push(c, LBM_BUF_A, c->stream[0]))) return rc;
+		CK(cudaEventRecord(c->ev_bnd[1], c->stream[0]));
+	}
+	for (int t = 0; t < nsteps; t++) {
+		const int src = t & 1, tail = t != nsteps - 1, cur = t & 1, prev = cur ^ 1;
+		for (int k = 0; k < n; k++) {
+			lbm_ctx *c = slabs[k], *up = slabs[(k + 1) % n], *dn = slabs[(k + n - 1) % n];
+			if ((rc = set_device(c))) return rc;
+			CK(cudaEventRecord(c->ev_main, c->stream[0]));
+			CK(cudaStreamWaitEvent(c->stream[1], c->ev_main, 0));
+			CK(cudaStreamWaitEvent(c->stream[1], up->ev_bnd[prev], 0));
+			CK(cudaStreamWaitEvent(c->stream[1], dn->ev_bnd[prev], 0));
+			if ((rc = launch_step(c, src, 0, 1, tail, c->stream[1]))) return rc;
+			if (c->nxl > 1 && (rc = launch_step(c, src, c->nxl - 1, c->nxl, tail, c->stream[1]))) return rc;
+		}
+		/* record after ALL slabs queued their waits on the previous events (an event re-recorded
+		 * before a neighbour's wait was enqueued would make that wait target the newer record) */
+		for (int k = 0; k < n; k++) {
+			lbm_ctx *c = slabs[k];
+			if ((rc = set_device(c))) return rc;
+			CK(cudaEventRecord(c->ev_bnd[cur], c->stream[1]));
+			if ((rc = launch_step(c, src, 1, c->nxl - 1, tail, c->stream[0]))) return rc;
+			CK(cudaStreamWaitEvent(c->stream[0], c->ev_bnd[cur], 0));
+		}
+	}
+	return LBM_OK;
+}
+
+int lbm_halo_pack(lbm_ctx *c, int buf, void *to_up, void *to_dn)
+{
+	if (!c || !to_up || !to_dn || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_halo_pack: bad argument");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	halo_pack_kernel<real_t><<<(c->ny + 255) / 256, 256, 0, c->stream[1]>>>(c->f[buf], (real_t *)to_up, (real_t *)to_dn, c->plane, c->ldy, c->nxl, c->ny);
+	CK(cudaGetLastError());
+	c->launches++;
+	return LBM_OK;
+}
+
+int lbm_halo_unpack(lbm_ctx *c, int buf, const void *from_dn, const void *from_up)
+{
+	if (!c || !from_dn || !from_up || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_halo_unpack: bad argument");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	halo_unpack_kernel<real_t><<<(c->ny + 255) / 256, 256, 0, c->stream[1]>>>(c->f[buf], (const real_t *)from_dn, (const real_t *)from_up, c->plane, c->ldy, c->nxl, c->ny);
+	CK(cudaGetLastError());
+	c->launches++;
+	return LBM_OK;
+}
+
+int lbm_step_rows(lbm_ctx *c, int src_buf, int r0, int r1, int tail_source, int stream_id)
+{
+	if (!c || (src_buf != 0 && src_buf != 1) || (stream_id != 0 && stream_id != 1)) return fail(LBM_ERR_ARG, "lbm_step_rows: bad argument");
+	if (r0 < 0 || r1 > c->nxl || r0 > r1) return fail(LBM_ERR_ARG, "lbm_step_rows: rows [%d,%d) of %d", r0, r1, c->nxl);
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	return launch_step(c, src_buf, r0, r1, tail_source, c->stream[stream_id]);
+}
+
+int lbm_stream_handle(lbm_ctx *c, int stream_id, void **out)
+{
+	if (!c || !out || (stream_id != 0 && stream_id != 1)) return fail(LBM_ERR_ARG, "lbm_stream_handle: bad argument");
+	*out = (void *)c->stream[stream_id];
+	return LBM_OK;
+}
+
+int lbm_stream_join(lbm_ctx *c)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_stream_join: null ctx");
+	int rc;
+	if ((rc = set_device(c))) return rc;
+	CK(cudaEventRecord(c->ev_bnd[0], c->stream[1]));
+	CK(cudaStreamWaitEvent(c->stream[0], c->ev_bnd[0], 0));
+	CK(cudaEventRecord(c->ev_main, c->stream[0]));
+	CK(cudaStreamWaitEvent(c->stream[1], c->ev_main, 0));
+	return LBM_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,586 @@
+// lbm_kernels.cuh -- sm_100a device code of the D2Q9 BGK timestep path.
+//
+// What it computes is StreamCollideVec / StreamCollide / ApplySource of the
+// reference (src/latticeboltzmann.c = "LB.c", lines cited at each function); how
+// it computes it is B200-first:
+//   * one fused pull kernel: stream + collide + bounce-back + body force of the
+//     NEXT step + halo push, A/B double buffer, SoA f[s][row][j] planes;
+//   * each thread owns V consecutive sites of one row (128-bit aligned vector
+//     loads/stores along j); the +-1 column neighbours of the six shifted
+//     streams come from the adjacent lane by warp shuffle, so every element of
+//     f is fetched from memory exactly once per step (144 B DP / 72 B SP per
+//     site update);
+//   * walls are a packed bitmask (1 bit/site); x-periodicity and the multi-GPU
+//     slab decomposition are the same mechanism: every slab carries two halo
+//     rows, and the threads of the first/last owned row store the three speeds
+//     the neighbour will pull (LB.c:237-243) straight into the neighbour's
+//     halo row -- a peer pointer over NVLink, or the slab itself when P == 1;
+//   * every floating-point operation is an explicit round-to-nearest intrinsic
+//     (__dadd_rn, __fmul_rn, ...): never contracted to FMA, evaluated in the
+//     reference's operation order, so DP and SP results are bit-identical to
+//     the reference's -O2 AVX build.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace lbm {
+
+// ---------------------------------------------------------------------------
+// correctly rounded, never-fused arithmetic in T
+// ---------------------------------------------------------------------------
+template <typename T> struct fp;
+template <> struct fp<double> {
+	static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+	static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+	static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+	static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
+};
+template <> struct fp<float> {
+	static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+	static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+	static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+	static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+};
+
+// ---------------------------------------------------------------------------
+// parameters of one launch
+// ---------------------------------------------------------------------------
+template <typename T> struct StepParams {
+	const T *src;          // source buffer, element (s=0, storage row 0, j=0)
+	T *dst;                // destination buffer
+	const uint32_t *mask;  // wall bits, [nxl][ldw] words, bit (j&31) of word j>>5
+	T *up_halo;            // neighbour above: (s=0, its storage row 0, j=0) of ITS dst buffer
+	T *dn_halo;            // neighbour below: (s=0, its storage row nxl'+1, j=0) of ITS dst buffer
+	size_t up_plane, dn_plane, plane;   // plane strides (elements)
+	int ldy, ldw;          // row strides: elements of T, mask words
+	int nxl, ny;           // owned rows, columns
+	int jmin, jmax;        // column range of this launch (vector kernel: [0,NYVECMAX))
+	int r0, r1;            // owned-row range of this launch
+	int vw;                // VECWIDTH of the reference build being matched
+	int tail_source;       // apply the NEXT step's ApplySource to column 0 before storing
+	T w0, w14, w58;        // OMEGA0/14/58 (LB.c:38-40), formed on the host in T
+	T itau;                // REAL_T(1.0)/TAU (LB.c:323)
+	double itau_d;         // (1.0/TAU) in double (LB.c:295,456)
+	T a14, a58;            // ACCEL*OMEGA14, ACCEL*OMEGA58 (LB.c:502-512)
+};
+
+// pull offsets (LB.c:235-243): speed -> (row shift, column shift)
+//   s : 0  1  2  3  4  5  6  7  8
+//   di: 0  0 -1  0 +1 -1 -1 +1 +1
+//   dj: 0 -1  0 +1  0 -1 +1 +1 -1
+__device__ __forceinline__ constexpr int pull_di(int s) { return (s == 2 || s == 5 || s == 6) ? -1 : (s == 4 || s == 7 || s == 8) ? 1 : 0; }
+__device__ __forceinline__ constexpr int pull_dj(int s) { return (s == 1 || s == 5 || s == 8) ? -1 : (s == 3 || s == 6 || s == 7) ? 1 : 0; }
+// bounce-back partner (LB.c:247-254)
+__device__ __forceinline__ constexpr int opposite(int s) { return s == 0 ? 0 : (s <= 4 ? ((s + 1) & 3) + 1 : ((s - 3) & 3) + 5); }
+
+// ---------------------------------------------------------------------------
+// vector memory access: V elements of T, V*sizeof(T) in {4,8,16,32} bytes
+// ---------------------------------------------------------------------------
+template <int HINT> __device__ __forceinline__ double ld1(const double *p)
+{
+	if (HINT == 0) return __ldg(p);
+	double v;
+	asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+	return v;
+}
+template <int HINT> __device__ __forceinline__ float ld1(const float *p)
+{
+	if (HINT == 0) return __ldg(p);
+	float v;
+	asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+	return v;
+}
+template <int HINT> __device__ __forceinline__ void ld16(const double *p, double &a, double &b)
+{
+	if (HINT == 0) { const double2 t = __ldg(reinterpret_cast<const double2 *>(p)); a = t.x; b = t.y; }
+	else asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(a), "=d"(b) : "l"(p));
+}
+template <int HINT> __device__ __forceinline__ void ld16(const float *p, float &a, float &b, float &c, float &d)
+{
+	if (HINT == 0) { const float4 t = __ldg(reinterpret_cast<const float4 *>(p)); a = t.x; b = t.y; c = t.z; d = t.w; }
+	else asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(p));
+}
+template <int HINT> __device__ __forceinline__ void ld8(const float *p, float &a, float &b)
+{
+	if (HINT == 0) { const float2 t = __ldg(reinterpret_cast<const float2 *>(p)); a = t.x; b = t.y; }
+	else asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "l"(p));
+}
+
+template <int HINT, int V> __device__ __forceinline__ void ldv(const double *p, double (&v)[V])
+{
+	if constexpr (V == 1) v[0] = ld1<HINT>(p);
+	else {
+#pragma unroll
+		for (int k = 0; k < V; k += 2) ld16<HINT>(p + k, v[k], v[k + 1]);
+	}
+}
+template <int HINT, int V> __device__ __forceinline__ void ldv(const float *p, float (&v)[V])
+{
+	if constexpr (V == 1) v[0] = ld1<HINT>(p);
+	else if constexpr (V == 2) ld8<HINT>(p, v[0], v[1]);
+	else {
+#pragma unroll
+		for (int k = 0; k < V; k += 4) ld16<HINT>(p + k, v[k], v[k + 1], v[k + 2], v[k + 3]);
+	}
+}
+
+template <int HINT> __device__ __forceinline__ void st1(double *p, double v)
+{
+	if (HINT == 0) *p = v; else __stcs(p, v);
+}
+template <int HINT> __device__ __forceinline__ void st1(float *p, float v)
+{
+	if (HINT == 0) *p = v; else __stcs(p, v);
+}
+template <int HINT, int V> __device__ __forceinline__ void stv(double *p, const double (&v)[V])
+{
+	if constexpr (V == 1) st1<HINT>(p, v[0]);
+	else {
+#pragma unroll
+		for (int k = 0; k < V; k += 2) {
+			const double2 t = make_double2(v[k], v[k + 1]);
+			if (HINT == 0) *reinterpret_cast<double2 *>(p + k) = t; else __stcs(reinterpret_cast<double2 *>(p + k), t);
+		}
+	}
+}
+template <int HINT, int V> __device__ __forceinline__ void stv(float *p, const float (&v)[V])
+{
+	if constexpr (V == 1) st1<HINT>(p, v[0]);
+	else if constexpr (V == 2) {
+		const float2 t = make_float2(v[0], v[1]);
+		if (HINT == 0) *reinterpret_cast<float2 *>(p) = t; else __stcs(reinterpret_cast<float2 *>(p), t);
+	} else {
+#pragma unroll
+		for (int k = 0; k < V; k += 4) {
+			const float4 t = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			if (HINT == 0) *reinterpret_cast<float4 *>(p + k) = t; else __stcs(reinterpret_cast<float4 *>(p + k), t);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
+// per-site arithmetic
+// ---------------------------------------------------------------------------
+
+// relaxation of the scalar statements LB.c:295 and 456-464: (feq-f) in T, the
+// product and the sum in double, rounded to T on store.
+template <typename T> __device__ __forceinline__ T relax_double(T f, T feq, double itau_d)
+{
+	const T d = fp<T>::sub(feq, f);
+	return (T)__dadd_rn((double)f, __dmul_rn(itau_d, (double)d));
+}
+
+// Fluid site, operation order of the SIMD path LB.c:360-451.
+// dbl != 0 selects the mixed-group fallback LB.c:455-465 (identical bits in DP).
+template <typename T>
+__device__ __forceinline__ void collide_vec_order(const T (&f)[9], T (&o)[9], const StepParams<T> &p, bool dbl)
+{
+	typedef fp<T> A;
+	T rho = A::add(T(0), f[0]);                                  // LB.c:360,372
+#pragma unroll
+	for (int s = 1; s < 9; s++) rho = A::add(rho, f[s]);         // LB.c:373-380
+	T ux = A::add(f[6], f[2]);                                   // LB.c:382-387
+	ux = A::add(ux, f[5]); ux = A::sub(ux, f[7]); ux = A::sub(ux, f[4]); ux = A::sub(ux, f[8]);
+	ux = A::div(ux, rho);
+	T uy = A::add(f[5], f[1]);                                   // LB.c:389-394
+	uy = A::add(uy, f[8]); uy = A::sub(uy, f[6]); uy = A::sub(uy, f[3]); uy = A::sub(uy, f[7]);
+	uy = A::div(uy, rho);
+	// CSQ == 1 (LB.c:49): _ICSQ multiplications are exact identities and are dropped
+	const T usq = A::mul(T(1.5), A::add(A::mul(ux, ux), A::mul(uy, uy)));   // LB.c:397
+	ux = A::mul(ux, T(3));                                       // LB.c:400-401
+	uy = A::mul(uy, T(3));
+	const T sum = A::add(ux, uy), dif = A::sub(ux, uy);
+	T e[9];
+	e[0] = T(0);
+	e[1] = uy;      e[2] = ux;                                   // LB.c:402-409; (-1)*x == -x exactly
+	e[3] = -uy;     e[4] = -ux;
+	e[5] = sum;     e[6] = dif;
+	e[7] = -sum;    e[8] = -dif;
+	T q[9];
+	q[0] = A::sub(T(1), usq);                                    // LB.c:413
+#pragma unroll
+	for (int s = 1; s < 9; s++)                                  // LB.c:414-421
+		q[s] = A::add(T(1), A::add(e[s], A::sub(A::mul(T(0.5), A::mul(e[s], e[s])), usq)));
+	const T r0 = A::mul(p.w0, rho), r14 = A::mul(p.w14, rho), r58 = A::mul(p.w58, rho);   // LB.c:425-433
+#pragma unroll
+	for (int s = 0; s < 9; s++) {
+		const T feq = A::mul(q[s], s == 0 ? r0 : (s <= 4 ? r14 : r58));
+		if (sizeof(T) == 4 && dbl) o[s] = relax_double<T>(f[s], feq, p.itau_d);           // LB.c:456-464
+		else o[s] = A::add(f[s], A::mul(p.itau, A::sub(feq, f[s])));                      // LB.c:442-450
+	}
+}
+
+// Fluid site, rounding order of the scalar function StreamCollide LB.c:257-297.
+template <typename T>
+__device__ __forceinline__ void collide_scalar_order(const T (&f)[9], T (&o)[9], const StepParams<T> &p)
+{
+	typedef fp<T> A;
+	T rho = A::add(T(0), f[0]);
+#pragma unroll
+	for (int s = 1; s < 9; s++) rho = A::add(rho, f[s]);         // LB.c:258-261
+	const T ux = A::div(A::sub(A::add(A::add(f[6], f[2]), f[5]), A::add(A::add(f[7], f[4]), f[8])), rho);   // LB.c:263-264
+	const T uy = A::div(A::sub(A::add(A::add(f[5], f[1]), f[8]), A::add(A::add(f[6], f[3]), f[7])), rho);   // LB.c:265-266
+	const T usq = A::add(A::mul(ux, ux), A::mul(uy, uy));        // LB.c:268
+	T e[9];                                                      // LB.c:271-279
+	e[0] = T(0);
+	e[1] = uy;                e[2] = ux;
+	e[3] = -uy;               e[4] = -ux;
+	e[5] = A::add(ux, uy);    e[6] = A::sub(ux, uy);
+	e[7] = A::sub(-ux, uy);   e[8] = A::add(-ux, uy);
+	const T t3 = A::mul(T(1.5), usq);                            // REAL_T(3.0)/REAL_T(2.0)*uDotu (/CSQ exact)
+	const T r0 = A::mul(p.w0, rho), r14 = A::mul(p.w14, rho), r58 = A::mul(p.w58, rho);
+#pragma unroll
+	for (int s = 0; s < 9; s++) {
+		T g;
+		if (s == 0) g = A::sub(T(1), t3);                        // LB.c:283
+		else g = A::sub(A::add(A::add(T(1), A::mul(T(3), e[s])), A::mul(A::mul(T(4.5), e[s]), e[s])), t3);   // LB.c:284-291
+		const T feq = A::mul(s == 0 ? r0 : (s <= 4 ? r14 : r58), g);
+		o[s] = relax_double<T>(f[s], feq, p.itau_d);             // LB.c:294-296
+	}
+}
+
+// wall site: reflect (LB.c:246-255, 466-475); o[0] is never stored
+template <typename T> __device__ __forceinline__ void bounce(const T (&f)[9], T (&o)[9])
+{
+	o[0] = f[0];
+#pragma unroll
+	for (int s = 1; s < 9; s++) o[s] = f[opposite(s)];
+}
+
+// ApplySource (LB.c:489-518) on the nine values of one fluid site of column 0
+template <typename T> __device__ __forceinline__ void source_site(T (&o)[9], const StepParams<T> &p)
+{
+	typedef fp<T> A;
+	const T n6 = A::sub(o[6], p.a58), n3 = A::sub(o[3], p.a14), n7 = A::sub(o[7], p.a58);
+	if (n6 > T(0) && n3 > T(0) && n7 > T(0)) {
+		o[6] = n6; o[3] = n3; o[7] = n7;
+		o[5] = A::add(o[5], p.a58); o[1] = A::add(o[1], p.a14); o[8] = A::add(o[8], p.a58);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// the fused pull kernel (StreamCollideVec, LB.c:307-484, + tail ApplySource + halo push)
+//   V    sites per thread (contiguous in j, V*sizeof(T) <= 32 bytes)
+//   NB   0: +-1 column element from the adjacent lane (shuffle), 1: direct load
+//   HINT 0: default caching, 1: L1::no_allocate loads, .cs stores
+// Launch: 1-D grid, blockDim multiple of 32; grid-stride over (row, vector) pairs.
+// ---------------------------------------------------------------------------
+template <typename T, int V, int NB, int HINT>
+__global__ void __launch_bounds__(512)
+stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
+{
+	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
+	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t stride = gridDim.x * blockDim.x;
+
+	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {   // warp-uniform trip count
+		const uint32_t g0 = base + threadIdx.x;
+		const bool active = g0 < total;
+		const uint32_t g = active ? g0 : total - 1;          // idle lanes shadow the last vector (loads stay legal)
+		const uint32_t rr = g / nvec;
+		const uint32_t jv = g - rr * nvec;
+		const int r = p.r0 + (int)rr;                        // owned row; storage row r+1
+		const int j0 = p.jmin + (int)jv * V;
+
+		// wrapped columns of the two out-of-vector neighbours (LB.c:337-338)
+		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
+		const int jr = j0 + V == p.ny ? 0 : j0 + V;
+		const bool edge_l = (NB == 1) || V == 1 || lane == 0 || jv == 0;
+		const bool edge_r = (NB == 1) || V == 1 || lane == 31 || jv == nvec - 1;
+
+		const T *row[3];                                     // rows i-1, i, i+1 of the source (halo rows make the wrap)
+		row[0] = p.src + (size_t)r * p.ldy;
+		row[1] = row[0] + p.ldy;
+		row[2] = row[1] + p.ldy;
+
+		T f[9][V];
+#pragma unroll
+		for (int s = 0; s < 9; s++) {
+			const T *base_s = row[pull_di(s) + 1] + (size_t)s * p.plane;
+			if constexpr (V == 1) {
+				const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0;
+				f[s][0] = ld1<HINT>(base_s + jj);
+			} else {
+				T own[V];
+				ldv<HINT, V>(base_s + j0, own);
+				if (pull_dj(s) == 0) {
+#pragma unroll
+					for (int k = 0; k < V; k++) f[s][k] = own[k];
+				} else if (pull_dj(s) < 0) {                 // element k comes from column j0+k-1
+					T nb = T(0);
+					if (NB == 0) nb = __shfl_up_sync(0xffffffffu, own[V - 1], 1);
+					if (edge_l) nb = ld1<HINT>(base_s + jl);
+					f[s][0] = nb;
+#pragma unroll
+					for (int k = 1; k < V; k++) f[s][k] = own[k - 1];
+				} else {                                     // element k comes from column j0+k+1
+					T nb = T(0);
+					if (NB == 0) nb = __shfl_down_sync(0xffffffffu, own[0], 1);
+					if (edge_r) nb = ld1<HINT>(base_s + jr);
+					f[s][V - 1] = nb;
+#pragma unroll
+					for (int k = 0; k < V - 1; k++) f[s][k] = own[k + 1];
+				}
+			}
+		}
+
+		// wall bits of my V sites and of my aligned VECWIDTH group (LB.c:437-440)
+		const uint32_t word = __ldg(p.mask + (size_t)r * p.ldw + (j0 >> 5));
+		const uint32_t sh = (uint32_t)j0 & 31u;
+		const uint32_t bits = (word >> sh) & ((1u << V) - 1u);
+		bool dbl = false;
+		if (sizeof(T) == 4) dbl = ((word >> (sh & ~(uint32_t)(p.vw - 1))) & ((1u << p.vw) - 1u)) != 0u;
+
+		T o[9][V];
+#pragma unroll
+		for (int k = 0; k < V; k++) {
+			T fk[9], ok[9];
+#pragma unroll
+			for (int s = 0; s < 9; s++) fk[s] = f[s][k];
+			if ((bits >> k) & 1u) {
+				bounce<T>(fk, ok);
+			} else {
+				collide_vec_order<T>(fk, ok, p, dbl);
+				if (k == 0 && j0 == 0 && p.tail_source) source_site<T>(ok, p);
+			}
+#pragma unroll
+			for (int s = 0; s < 9; s++) o[s][k] = ok[s];
+		}
+
+		if (active) {
+			T *d = p.dst + (size_t)(r + 1) * p.ldy + j0;
+			if (bits == 0u) stv<HINT, V>(d, o[0]);
+			else {
+#pragma unroll
+				for (int k = 0; k < V; k++) if (!((bits >> k) & 1u)) d[k] = o[0][k];     // f0 untouched at walls
+			}
+#pragma unroll
+			for (int s = 1; s < 9; s++) stv<HINT, V>(d + (size_t)s * p.plane, o[s]);
+			if (r == 0) {                                    // what the slab below pulls from its row "hi" (LB.c:239,242,243)
+				stv<HINT, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
+				stv<HINT, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
+				stv<HINT, V>(p.dn_halo + 8 * p.dn_plane + j0, o[8]);
+			}
+			if (r == p.nxl - 1) {                            // what the slab above pulls from its row "lo-1" (LB.c:237,240,241)
+				stv<HINT, V>(p.up_halo + 2 * p.up_plane + j0, o[2]);
+				stv<HINT, V>(p.up_halo + 5 * p.up_plane + j0, o[5]);
+				stv<HINT, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
+			}
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
+// scalar-order kernel: StreamCollide (LB.c:216-302) for columns [jmin,jmax) --
+// the ragged tail j >= NYVECMAX of a vector build, or everything when the
+// matched reference build is a prec_*_serial.h one.  One site per thread.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+stream_collide_scalar_kernel(const __grid_constant__ StepParams<T> p)
+{
+	const uint32_t ncol = (uint32_t)(p.jmax - p.jmin);
+	const uint32_t total = (uint32_t)(p.r1 - p.r0) * ncol;
+	for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
+		const uint32_t rr = g / ncol;
+		const int r = p.r0 + (int)rr;
+		const int j = p.jmin + (int)(g - rr * ncol);
+		const int jl = j == 0 ? p.ny - 1 : j - 1;
+		const int jr = j + 1 == p.ny ? 0 : j + 1;
+		const T *row0 = p.src + (size_t)r * p.ldy;
+		T f[9], o[9];
+#pragma unroll
+		for (int s = 0; s < 9; s++) {
+			const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j;
+			f[s] = __ldg(row0 + (size_t)(pull_di(s) + 1) * p.ldy + (size_t)s * p.plane + jj);
+		}
+		const bool wall = (__ldg(p.mask + (size_t)r * p.ldw + (j >> 5)) >> (j & 31)) & 1u;
+		if (wall) bounce<T>(f, o);
+		else {
+			collide_scalar_order<T>(f, o, p);
+			if (j == 0 && p.tail_source) source_site<T>(o, p);
+		}
+		T *d = p.dst + (size_t)(r + 1) * p.ldy + j;
+		if (!wall) d[0] = o[0];
+#pragma unroll
+		for (int s = 1; s < 9; s++) d[(size_t)s * p.plane] = o[s];
+		if (r == 0) {
+			p.dn_halo[4 * p.dn_plane + j] = o[4]; p.dn_halo[7 * p.dn_plane + j] = o[7]; p.dn_halo[8 * p.dn_plane + j] = o[8];
+		}
+		if (r == p.nxl - 1) {
+			p.up_halo[2 * p.up_plane + j] = o[2]; p.up_halo[5 * p.up_plane + j] = o[5]; p.up_halo[6 * p.up_plane + j] = o[6];
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
+// small kernels around the step
+// ---------------------------------------------------------------------------
+
+// ApplySource (LB.c:489-518), in place on column 0 of owned rows of one buffer.
+template <typename T>
+__global__ void apply_source_kernel(T *f, const StepParams<T> p)
+{
+	const int r = blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= p.nxl) return;
+	if (__ldg(p.mask + (size_t)r * p.ldw) & 1u) return;          // walls[I(i,0,0)] != 0
+	T *site = f + (size_t)(r + 1) * p.ldy;
+	T v[9];
+	v[0] = T(0);
+#pragma unroll
+	for (int s = 1; s < 9; s++) v[s] = site[(size_t)s * p.plane];
+	source_site<T>(v, p);
+	site[1 * p.plane] = v[1]; site[3 * p.plane] = v[3]; site[5 * p.plane] = v[5];
+	site[6 * p.plane] = v[6]; site[7 * p.plane] = v[7]; site[8 * p.plane] = v[8];
+}
+
+// Copy the halo speeds of the first/last owned row of `f` into the neighbours' halo rows
+// (same destinations as the fused push in the step kernel).
+template <typename T>
+__global__ void halo_push_kernel(const T *f, const StepParams<T> p)
+{
+	const int j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= p.ny) return;
+	const T *lo = f + (size_t)1 * p.ldy + j, *hi = f + (size_t)p.nxl * p.ldy + j;
+	p.dn_halo[4 * p.dn_plane + j] = lo[4 * p.plane];
+	p.dn_halo[7 * p.dn_plane + j] = lo[7 * p.plane];
+	p.dn_halo[8 * p.dn_plane + j] = lo[8 * p.plane];
+	p.up_halo[2 * p.up_plane + j] = hi[2 * p.plane];
+	p.up_halo[5 * p.up_plane + j] = hi[5 * p.plane];
+	p.up_halo[6 * p.up_plane + j] = hi[6 * p.plane];
+}
+
+// Staged exchange: messages are [3][ny] contiguous.  to_up = speeds 2,5,6 of the last owned
+// row, to_dn = speeds 4,7,8 of the first owned row.
+template <typename T>
+__global__ void halo_pack_kernel(const T *f, T *to_up, T *to_dn, size_t plane, int ldy, int nxl, int ny)
+{
+	const int j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= ny) return;
+	const T *lo = f + (size_t)1 * ldy + j, *hi = f + (size_t)nxl * ldy + j;
+	to_up[j] = hi[2 * plane]; to_up[ny + j] = hi[5 * plane]; to_up[2 * (size_t)ny + j] = hi[6 * plane];
+	to_dn[j] = lo[4 * plane]; to_dn[ny + j] = lo[7 * plane]; to_dn[2 * (size_t)ny + j] = lo[8 * plane];
+}
+template <typename T>
+__global__ void halo_unpack_kernel(T *f, const T *from_dn, const T *from_up, size_t plane, int ldy, int nxl, int ny)
+{
+	const int j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= ny) return;
+	T *lo = f + j, *hi = f + (size_t)(nxl + 1) * ldy + j;            // halo rows: storage 0 and nxl+1
+	lo[2 * plane] = from_dn[j]; lo[5 * plane] = from_dn[ny + j]; lo[6 * plane] = from_dn[2 * (size_t)ny + j];
+	hi[4 * plane] = from_up[j]; hi[7 * plane] = from_up[ny + j]; hi[8 * plane] = from_up[2 * (size_t)ny + j];
+}
+
+// Scene description, evaluated per site (InitializeArrays, LB.c:559-578, plus a disc)
+struct SceneDev {
+	int nx, channel_walls;
+	int bar_i0, bar_i1, bar_j0, bar_j1;
+	long long disc_ci, disc_cj, disc_r2;   // disc_r2 < 0: none
+};
+__device__ __forceinline__ bool scene_is_wall(const SceneDev &sc, int gi, int j)
+{
+	if (sc.channel_walls && (gi == 0 || gi == sc.nx - 1)) return true;
+	if (gi >= sc.bar_i0 && gi < sc.bar_i1 && j >= sc.bar_j0 && j < sc.bar_j1) return true;
+	if (sc.disc_r2 >= 0) {
+		const long long di = gi - sc.disc_ci, dj = j - sc.disc_cj;
+		if (di * di + dj * dj <= sc.disc_r2) return true;
+	}
+	return false;
+}
+// one thread per mask word
+__global__ void scene_mask_kernel(uint32_t *mask, SceneDev sc, int row_lo, int nxl, int ny, int ldw)
+{
+	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= (size_t)nxl * ldw) return;
+	const int r = (int)(g / ldw), w = (int)(g % ldw);
+	uint32_t bits = 0;
+	for (int b = 0; b < 32; b++) {
+		const int j = w * 32 + b;
+		if (j < ny && scene_is_wall(sc, row_lo + r, j)) bits |= 1u << b;
+	}
+	mask[g] = bits;
+}
+// fA = rho0*omega_s at every owned site (walls included), fB = 0 (LB.c:580-603); j < ny only
+template <typename T>
+__global__ void scene_fill_kernel(T *fA, T *fB, size_t plane, int ldy, int nxl, int ny, T v0, T v14, T v58)
+{
+	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= (size_t)nxl * ny) return;
+	const int r = (int)(g / ny), j = (int)(g % ny);
+	const size_t o = (size_t)(r + 1) * ldy + j;
+#pragma unroll
+	for (int s = 0; s < 9; s++) {
+		fA[o + s * plane] = s == 0 ? v0 : (s <= 4 ? v14 : v58);
+		fB[o + s * plane] = T(0);
+	}
+}
+
+// walls chars [nxl][ldc] -> bit words; *bad is set if a value other than 0/1 is seen
+__global__ void mask_pack_kernel(const char *walls, size_t ldc, uint32_t *mask, int nxl, int ny, int ldw, int *bad)
+{
+	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= (size_t)nxl * ldw) return;
+	const int r = (int)(g / ldw), w = (int)(g % ldw);
+	uint32_t bits = 0;
+	for (int b = 0; b < 32; b++) {
+		const int j = w * 32 + b;
+		if (j < ny) {
+			const char c = walls[(size_t)r * ldc + j];
+			if (c == 1) bits |= 1u << b; else if (c != 0) *bad = 1;
+		}
+	}
+	mask[g] = bits;
+}
+__global__ void mask_unpack_kernel(const uint32_t *mask, char *walls, size_t ldc, int nxl, int ny, int ldw)
+{
+	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= (size_t)nxl * ny) return;
+	const int r = (int)(g / ny), j = (int)(g % ny);
+	walls[(size_t)r * ldc + j] = (char)((mask[(size_t)r * ldw + (j >> 5)] >> (j & 31)) & 1u);
+}
+
+// rho, u_x, u_y in the order of PrintLattice / ComputeReynolds (LB.c:621-629, 535-540).
+// Dense outputs [nxl][ncol]; column range [j0, j0+ncol).
+template <typename T>
+__global__ void macroscopic_kernel(const T *f, size_t plane, int ldy, int nxl, int j0, int ncol, T *rho_o, T *ux_o, T *uy_o)
+{
+	typedef fp<T> A;
+	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= (size_t)nxl * ncol) return;
+	const int r = (int)(g / ncol), j = j0 + (int)(g % ncol);
+	const T *site = f + (size_t)(r + 1) * ldy + j;
+	T v[9], rho = T(0);
+#pragma unroll
+	for (int s = 0; s < 9; s++) { v[s] = site[(size_t)s * plane]; rho = A::add(rho, v[s]); }
+	if (rho_o) rho_o[g] = rho;
+	if (ux_o) ux_o[g] = A::div(A::sub(A::add(A::add(v[6], v[2]), v[5]), A::add(A::add(v[7], v[4]), v[8])), rho);
+	if (uy_o) uy_o[g] = A::div(A::sub(A::add(A::add(v[5], v[1]), v[8]), A::add(A::add(v[6], v[3]), v[7])), rho);
+}
+
+// ---- neighbour barrier between ranks living in different processes / GPUs ----
+// signal: my epoch into the slot each neighbour reserves for me.  Runs after the boundary
+// kernel in stream order, so the halo stores it announces have been performed.
+__global__ void flag_signal_kernel(volatile int *up_slot, volatile int *dn_slot, int epoch)
+{
+	__threadfence_system();
+	*up_slot = epoch;
+	*dn_slot = epoch;
+	__threadfence_system();
+}
+// wait: spin until both neighbours have announced `epoch`.  The spinners live on DIFFERENT
+// GPUs than the signallers.  Gives up after ~timeout_ns and raises flags[3].
+__global__ void flag_wait_kernel(volatile int *flags, int epoch, unsigned long long timeout_ns)
+{
+	unsigned long long t0;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+	while (flags[0] < epoch || flags[1] < epoch) {
+		unsigned long long t;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+		if (t - t0 > timeout_ns) { flags[3] = 1; break; }
+		__nanosleep(200);
+	}
+	__threadfence_system();
+}
+
+} // namespace lbm
