@@ -86,6 +86,10 @@ int lbm_upload(lbm_ctx *ctx, const real_t *fA, const real_t *fB, const char *wal
 /* Copies this slab's rows into global-layout host arrays; either pointer may be NULL.
  * walls_out (optional) receives the unpacked device bitmask as chars. */
 int lbm_download(lbm_ctx *ctx, real_t *fA, real_t *fB, char *walls_out, int ldy);
+/* Same, for host arrays that hold ONLY this slab's rows (what one MPI rank of the reference
+ * would own): planes of nx_local rows, the slab's first row at row 0. */
+int lbm_upload_slab(lbm_ctx *ctx, const real_t *fA, const real_t *fB, const char *walls, int ldy);
+int lbm_download_slab(lbm_ctx *ctx, real_t *fA, real_t *fB, char *walls_out, int ldy);
 
 /* ---- the timestep path ---- */
 /* DoTimeStep (LB.c:186-210): Source(A); A->B; Source(B); B->A.  Asynchronous. */

@@ -51,7 +51,7 @@ def _structs(real):
 # every symbol include/lbm_b200.h declares (tests check the library exports each one)
 SYMBOLS = [
     "lbm_sizeof_real", "lbm_last_error", "lbm_version", "lbm_create", "lbm_destroy",
-    "lbm_scene_reference", "lbm_initialize_arrays", "lbm_upload", "lbm_download",
+    "lbm_scene_reference", "lbm_initialize_arrays", "lbm_upload", "lbm_download", "lbm_upload_slab", "lbm_download_slab",
     "lbm_do_timestep", "lbm_run", "lbm_run_timed", "lbm_apply_source", "lbm_stream_collide", "lbm_sync",
     "lbm_compute_reynolds", "lbm_reynolds_column", "lbm_reynolds_from_column", "lbm_macroscopic",
     "lbm_print_lattice", "lbm_slab_info_get", "lbm_ipc_export", "lbm_ipc_connect", "lbm_connect_local",
@@ -87,6 +87,7 @@ class Lib:
         for name, args in {
             "lbm_destroy": [vp], "lbm_initialize_arrays": [vp, ctypes.POINTER(self.Scene)],
             "lbm_upload": [vp, vp, vp, vp, ci], "lbm_download": [vp, vp, vp, vp, ci],
+            "lbm_upload_slab": [vp, vp, vp, vp, ci], "lbm_download_slab": [vp, vp, vp, vp, ci],
             "lbm_do_timestep": [vp], "lbm_run": [vp, ci], "lbm_run_timed": [vp, ci, ctypes.POINTER(ctypes.c_float)],
             "lbm_apply_source": [vp, ci], "lbm_stream_collide": [vp, ci], "lbm_sync": [vp],
             "lbm_compute_reynolds": [vp, ctypes.POINTER(self.real)], "lbm_reynolds_column": [vp, vp, vp],

@@ -417,15 +417,16 @@ int lbm_initialize_arrays(lbm_ctx *c, const lbm_scene *scene)
 	return LBM_OK;
 }
 
-int lbm_upload(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *walls, int ldy)
+/* host arrays hold `host_rows` lattice rows per plane; the slab's first row is host row `first` */
+static int upload_impl(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *walls, int ldy, int host_rows, int first)
 {
 	if (!c || !fA || !walls) return fail(LBM_ERR_ARG, "lbm_upload: null argument");
 	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_upload: ldy %d < ny %d", ldy, c->ny);
 	int rc;
 	if ((rc = set_device(c))) return rc;
 	cudaStream_t st = c->stream[0];
-	const size_t hplane = (size_t)c->cfg.nx * ldy;              /* host plane stride, I() of LB.c:72 */
-	const size_t row0 = (size_t)c->cfg.row_lo * ldy;
+	const size_t hplane = (size_t)host_rows * ldy;              /* host plane stride, I() of LB.c:72 */
+	const size_t row0 = (size_t)first * ldy;
 	for (int b = 0; b < 2; b++) {
 		const real_t *src = b == 0 ? fA : fB;
 		if (!src) {                                              /* fB = 0 (LB.c:593-601) */
@@ -459,14 +460,26 @@ int lbm_upload(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *walls
 	return LBM_OK;
 }
 
-int lbm_download(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy)
+int lbm_upload(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *walls, int ldy)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_upload: null ctx");
+	return upload_impl(c, fA, fB, walls, ldy, c->cfg.nx, c->cfg.row_lo);
+}
+
+int lbm_upload_slab(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *walls, int ldy)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_upload_slab: null ctx");
+	return upload_impl(c, fA, fB, walls, ldy, c->nxl, 0);
+}
+
+static int download_impl(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy, int host_rows, int first)
 {
 	if (!c) return fail(LBM_ERR_ARG, "lbm_download: null ctx");
 	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_download: ldy %d < ny %d", ldy, c->ny);
 	int rc;
 	if ((rc = lbm_sync(c))) return rc;
 	cudaStream_t st = c->stream[0];
-	const size_t hplane = (size_t)c->cfg.nx * ldy, row0 = (size_t)c->cfg.row_lo * ldy;
+	const size_t hplane = (size_t)host_rows * ldy, row0 = (size_t)first * ldy;
 	for (int b = 0; b < 2; b++) {
 		real_t *dst = b == 0 ? fA : fB;
 		if (!dst) continue;
@@ -487,6 +500,18 @@ int lbm_download(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy)
 	}
 	CK(cudaStreamSynchronize(st));
 	return LBM_OK;
+}
+
+int lbm_download(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_download: null ctx");
+	return download_impl(c, fA, fB, walls_out, ldy, c->cfg.nx, c->cfg.row_lo);
+}
+
+int lbm_download_slab(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_download_slab: null ctx");
+	return download_impl(c, fA, fB, walls_out, ldy, c->nxl, 0);
 }
 
 // ---------------------------------------------------------------------------

@@ -38,6 +38,21 @@ def ring_neighbours(rank, world):
     return (rank + 1) % world, (rank - 1) % world
 
 
+def pack_messages(f_ext):
+    """Host statement of the message layout (mirrors halo_pack_kernel): ``f_ext`` is (9, nxl+2, ny) with
+    halo rows 0 and nxl+1.  Returns (to_up, to_dn), each (3, ny): the last owned row's speeds 2,5,6 and
+    the first owned row's speeds 4,7,8."""
+    return (np.ascontiguousarray(f_ext[list(HALO_UP_SPEEDS), -2, :]),
+            np.ascontiguousarray(f_ext[list(HALO_DN_SPEEDS), 1, :]))
+
+
+def unpack_messages(f_ext, from_dn, from_up):
+    """Mirrors halo_unpack_kernel: what the slab below sent up lands in the lower halo row (speeds
+    2,5,6), what the slab above sent down lands in the upper halo row (speeds 4,7,8)."""
+    f_ext[list(HALO_UP_SPEEDS), 0, :] = from_dn
+    f_ext[list(HALO_DN_SPEEDS), -1, :] = from_up
+
+
 def exchange_halos(to_up, to_dn, from_dn, from_up, rank, world, group=None):
     """One ring exchange of packed halo messages (torch tensors; CPU/gloo or CUDA/NCCL).
 

@@ -79,6 +79,23 @@ class Lattice:
         self._call("lbm_download", a, b, None, ldy)
         return out
 
+    def upload_slab(self, fA, walls, fB=None):
+        """Host arrays holding only this slab's rows: fA (9,nx_local,ny), walls (nx_local,ny)."""
+        assert fA.flags.c_contiguous and fA.dtype == self.dtype and fA.size == 9 * self.nx_local * self.ny
+        walls = np.ascontiguousarray(walls, dtype=np.int8)
+        self._call("lbm_upload_slab", _ptr(fA), _ptr(fB), _ptr(walls), self.ny)
+
+    def download_slab(self, out=None, which="A", walls=False):
+        if walls:
+            w = np.zeros((self.nx_local, self.ny), dtype=np.int8)
+            self._call("lbm_download_slab", None, None, _ptr(w), self.ny)
+            return w
+        if out is None:
+            out = np.zeros((9, self.nx_local, self.ny), dtype=self.dtype)
+        a, b = (_ptr(out), None) if which == "A" else (None, _ptr(out))
+        self._call("lbm_download_slab", a, b, None, self.ny)
+        return out
+
     def download_walls(self, ldy=None):
         ldy = self.ny if ldy is None else ldy
         out = np.zeros((self.nx, ldy), dtype=np.int8)

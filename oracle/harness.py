@@ -110,6 +110,14 @@ class Oracle(_Base):
         f = self.fA if which == "A" else self.fB
         self.lib.lbo_apply_source(ctypes.byref(self.p), self._p(f), self._p(self.walls))
 
+    def stream_collide(self, src="A"):
+        """One pull step src -> other buffer WITHOUT the source term (LB.c:195-196)."""
+        a, b = (self.fA, self.fB) if src == "A" else (self.fB, self.fA)
+        nyvec = self.vw * (self.ny // self.vw) if self.vw > 1 else 0
+        if nyvec:
+            self.lib.lbo_stream_collide_vec(ctypes.byref(self.p), 0, nyvec, self._p(a), self._p(b), self._p(self.walls))
+        self.lib.lbo_stream_collide(ctypes.byref(self.p), nyvec, self.ny, self._p(a), self._p(b), self._p(self.walls))
+
     def reynolds(self):
         return float(self.lib.lbo_compute_reynolds(ctypes.byref(self.p), self._p(self.fA), self._p(self.walls)))
 

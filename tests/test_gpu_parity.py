@@ -1,0 +1,268 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on the same
+inputs, against the golden vectors of the compiled reference, and through size-independent
+properties at BASELINE.json's full sizes.
+
+Tolerances: NONE.  f_i, the Reynolds number, rho/u and the wall mask are compared bit for bit
+(stricter than north_star's 1e-12 DP / 1e-5 SP), because the kernels evaluate every operation
+in the reference's order with round-to-nearest intrinsics."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from tests import cases
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))
+VW = {("dp", "avx"): 4, ("dp", "sse"): 2, ("dp", "serial"): 1, ("sp", "avx"): 8, ("sp", "sse"): 4, ("sp", "serial"): 1}
+
+
+def _lattice(c, **kw):
+    from latticeboltzmann_b200 import Lattice
+    return Lattice(c["nx"], c["ny"], c["prec"], vecwidth=VW[(c["prec"], c["isa"])], **kw)
+
+
+def _oracle(c, fA, walls, steps):
+    from oracle.harness import Oracle
+    o = Oracle(c["prec"], c["nx"], c["ny"], VW[(c["prec"], c["isa"])])
+    o.set_state(fA, walls)
+    o.run(steps)
+    return o
+
+
+def _assert_same(got, want, what):
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape and got.dtype == want.dtype, f"{what}: {got.shape}/{got.dtype} vs {want.shape}/{want.dtype}"
+    if got.tobytes() != want.tobytes():
+        bad = np.argwhere(~((got == want) & (np.signbit(got) == np.signbit(want))))
+        at = tuple(bad[0]) if len(bad) else None
+        raise AssertionError(f"{what}: {len(bad)} elements differ, first at {at}: "
+                             f"{got[at]!r} vs {want[at]!r}" if at else f"{what}: bytes differ")
+
+
+# ---------------------------------------------------------------------------------------------
+# against the golden vectors of the compiled reference (every case, incl. 10,000 steps)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_cuda_matches_reference_golden(name):
+    c, g = cases.CASES[name], GOLDEN[name]
+    fA, walls = cases.make_inputs(name)
+    with _lattice(c) as lat:
+        lat.upload(fA, walls)
+        lat.run(c["steps"])
+        a, b = lat.download("A"), lat.download("B")
+        assert cases.digest(a) == g["fA_sha256"], f"fA differs from the reference after {c['steps']} steps"
+        assert cases.digest(b) == g["fB_sha256"], "fB differs (odd step with its source applied, LB.c:201)"
+        assert float(lat.ComputeReynolds()).hex() == g["reynolds_hex"]
+        _assert_same(lat.download_walls(), walls, "wall mask round trip")
+        if c.get("full"):
+            z = np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz"))
+            _assert_same(a, z["fA"], "fA")
+            _assert_same(b, z["fB"], "fB")
+
+
+# ---------------------------------------------------------------------------------------------
+# against the oracle, over kernel variants and awkward shapes
+# ---------------------------------------------------------------------------------------------
+SHAPES = [
+    dict(nx=3, ny=8), dict(nx=1, ny=16), dict(nx=2, ny=9), dict(nx=5, ny=33), dict(nx=40, ny=64),
+    dict(nx=33, ny=257), dict(nx=64, ny=1000), dict(nx=7, ny=4099),
+]
+
+
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+@pytest.mark.parametrize("isa", ["avx", "sse", "serial"])
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: f"{s['nx']}x{s['ny']}")
+def test_cuda_matches_oracle_shapes(prec, isa, shape):
+    c = dict(prec=prec, isa=isa, scene="random", perturb=31, steps=8, **shape)
+    fA, walls = cases.make_inputs(c)
+    if c["nx"] < 3:
+        walls[:] = 0                           # no channel rows when the lattice is 1-2 rows high
+        walls[0, ::5] = 1
+    o = _oracle(c, fA, walls, c["steps"])
+    with _lattice(c) as lat:
+        lat.upload(fA, walls)
+        lat.run(c["steps"])
+        _assert_same(lat.download("A"), o.f_view("A"), "fA")
+        _assert_same(lat.download("B"), o.f_view("B"), "fB")
+
+
+def _variants(prec):
+    vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
+    out = []
+    for v in vecs:
+        for nb in (0, 1):
+            for hints in (0, 1):
+                out.append(dict(vec=v, neighbour=nb, hints=hints, block=256, ctas_per_sm=0))
+    out += [dict(vec=vecs[-1], neighbour=0, hints=0, block=128, ctas_per_sm=2),
+            dict(vec=2, neighbour=0, hints=1, block=512, ctas_per_sm=1),
+            dict(vec=2, neighbour=0, hints=0, block=64, ctas_per_sm=8)]
+    return out
+
+
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+def test_every_kernel_variant_is_bit_identical(prec):
+    c = dict(prec=prec, isa="avx", nx=96, ny=520, scene="random", perturb=17, steps=10)
+    fA, walls = cases.make_inputs(c)
+    o = _oracle(c, fA, walls, c["steps"])
+    with _lattice(c) as lat:
+        for tune in _variants(prec):
+            lat.set_tuning(**tune)
+            lat.upload(fA, walls)
+            lat.run(c["steps"])
+            _assert_same(lat.download("A"), o.f_view("A"), f"fA with {tune}")
+            _assert_same(lat.download("B"), o.f_view("B"), f"fB with {tune}")
+
+
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+def test_reference_function_surface(prec):
+    """DoTimeStep == ApplySource/StreamCollide x2 (LB.c:186-210); InitializeArrays on the device ==
+    the host scene; ComputeReynolds, macroscopic fields and PrintLattice as the oracle computes them."""
+    from latticeboltzmann_b200 import Lattice
+    from oracle.harness import Oracle
+    nx, ny = 230, 136
+    o = Oracle(prec, nx, ny)
+    o.initialize()
+    with Lattice(nx, ny, prec) as a, Lattice(nx, ny, prec) as b:
+        a.InitializeArrays()
+        _assert_same(a.download("A"), o.f_view("A"), "InitializeArrays fA")
+        _assert_same(a.download_walls(), o.walls_view(), "InitializeArrays walls")
+        b.upload(o.f_view("A"), o.walls_view())
+        for _ in range(3):
+            a.DoTimeStep()
+            b.ApplySource("A"); b.StreamCollide("A"); b.ApplySource("B"); b.StreamCollide("B")
+        o.run(6)
+        _assert_same(a.download("A"), o.f_view("A"), "DoTimeStep x3")
+        _assert_same(b.download("A"), o.f_view("A"), "ApplySource/StreamCollide x6")
+        _assert_same(a.download("B"), o.f_view("B"), "fB")
+        assert a.ComputeReynolds() == o.reynolds()
+        for got, want, nm in zip(a.macroscopic(), o.macroscopic(), ("rho", "ux", "uy")):
+            _assert_same(got, want, nm)
+
+
+def test_print_lattice_bytes(tmp_path):
+    from latticeboltzmann_b200 import Lattice
+    from oracle.harness import Oracle
+    for prec in ("dp", "sp"):
+        nx, ny = 230, 120
+        o = Oracle(prec, nx, ny)
+        o.initialize()
+        o.run(40)
+        with Lattice(nx, ny, prec) as lat:
+            lat.InitializeArrays()
+            lat.run(40)
+            lat.PrintLattice(tmp_path / f"gpu_{prec}.csv")
+        o.print_lattice(str(tmp_path / f"cpu_{prec}.csv"))
+        assert (tmp_path / f"gpu_{prec}.csv").read_bytes() == (tmp_path / f"cpu_{prec}.csv").read_bytes()
+
+
+def test_error_behaviour():
+    from latticeboltzmann_b200 import Lattice, LbmError
+    with Lattice(8, 16) as lat:
+        with pytest.raises(LbmError):
+            lat.run(2)                                   # nothing loaded
+        f, w = np.zeros((9, 8, 16)), np.zeros((8, 16), dtype=np.int8)
+        w[3, 3] = 2
+        with pytest.raises(LbmError):
+            lat.upload(f + 0.1, w)                       # mask must be 0/1
+        w[3, 3] = 1
+        lat.upload(f + 0.1, w)
+        with pytest.raises(LbmError):
+            lat.run(3)                                   # odd step count (LB.c:148)
+        lat.run(0)
+    with pytest.raises(LbmError):
+        Lattice(0, 16)
+
+
+# ---------------------------------------------------------------------------------------------
+# decomposition invariance: N logical slabs on one GPU == one slab, bit for bit
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("prec,nslabs", [("dp", 2), ("dp", 3), ("dp", 8), ("sp", 4)])
+def test_slab_ring_equals_single_slab(prec, nslabs):
+    from latticeboltzmann_b200 import Lattice, group_run, make_ring
+    c = dict(prec=prec, isa="avx", nx=200, ny=1000, scene="cylinder", perturb=None, steps=60)
+    fA, walls = cases.make_inputs(c)
+    with Lattice(c["nx"], c["ny"], prec) as one:
+        one.upload(fA, walls)
+        one.run(c["steps"])
+        want_a, want_b, want_re = one.download("A"), one.download("B"), one.ComputeReynolds()
+    ring = make_ring(c["nx"], c["ny"], nslabs, prec)
+    try:
+        for s in ring:
+            s.upload(fA, walls)
+        group_run(ring, 20)
+        group_run(ring, 40)
+        got_a, got_b = np.zeros_like(want_a), np.zeros_like(want_b)
+        for s in ring:
+            s.download("A", out=got_a)
+            s.download("B", out=got_b)
+        _assert_same(got_a, want_a, "fA over the ring")
+        _assert_same(got_b, want_b, "fB over the ring")
+        cols = [s.reynolds_column() for s in ring]
+        re = ring[0].reynolds_from_column(np.concatenate([u for u, _ in cols]), np.concatenate([f for _, f in cols]))
+        assert re == want_re
+    finally:
+        for s in ring:
+            s.close()
+
+
+def test_uneven_slabs_and_single_row_slabs():
+    from latticeboltzmann_b200 import Lattice, group_run, make_ring
+    c = dict(prec="dp", isa="avx", nx=11, ny=64, scene="random", perturb=9, steps=10)
+    fA, walls = cases.make_inputs(c)
+    o = _oracle(c, fA, walls, c["steps"])
+    for bounds in ([(0, 1), (1, 2), (2, 11)], [(0, 5), (5, 6), (6, 11)], [(k, k + 1) for k in range(11)]):
+        ring = make_ring(c["nx"], c["ny"], len(bounds), "dp", bounds=bounds)
+        try:
+            for s in ring:
+                s.upload(fA, walls)
+            group_run(ring, c["steps"])
+            got = np.zeros_like(fA)
+            for s in ring:
+                s.download("A", out=got)
+            _assert_same(got, o.f_view("A"), f"ring {bounds}")
+        finally:
+            for s in ring:
+                s.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# full BASELINE sizes: properties that need no CPU run
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+def test_full_size_properties_400x4000(prec):
+    """BASELINE config 2 at its full 10,000 steps: mass is conserved to rounding (source and
+    bounce-back are conservative), wall-site f0 keeps its initial value (LB.c:246-255), the flow is
+    finite and positive, and two chunked runs equal one long run bit for bit."""
+    from latticeboltzmann_b200 import Lattice
+    nx, ny, steps = 400, 4000, 10000
+    with Lattice(nx, ny, prec) as a, Lattice(nx, ny, prec) as b:
+        a.InitializeArrays()
+        b.InitializeArrays()
+        f0 = a.download("A")
+        walls = a.download_walls().astype(bool)
+        a.run(steps)
+        for _ in range(10):
+            b.run(steps // 10)
+        fa, fb = a.download("A"), b.download("A")
+        assert fa.tobytes() == fb.tobytes()
+        assert np.isfinite(fa).all() and (fa[:, ~walls] > 0).all()
+        m0, m1 = f0.astype(np.float64).sum(), fa.astype(np.float64).sum()
+        assert abs(m1 - m0) / m0 < (1e-11 if prec == "dp" else 2e-3)
+        np.testing.assert_array_equal(fa[0][walls], f0[0][walls])
+        assert np.isfinite(a.ComputeReynolds())
+
+
+def test_c_driver_prints_reference_reynolds():
+    """driver/main.c (the reference's main over the C ABI) on the shipped scenario: the final line's
+    Re must be the compiled reference's value to all printed digits (LB.c:173, %.10le)."""
+    for tag, case in (("dp", "builtin_dp_10000"), ("sp", "builtin_sp_10000")):
+        exe = os.path.join(ROOT, "driver", f"lbm_b200_{tag}")
+        out = subprocess.run([exe, "400", "2000", "10000"], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr
+        last = out.stdout.strip().splitlines()[-1]
+        want = "%.10le" % float.fromhex(GOLDEN[case]["reynolds_hex"])
+        assert last.startswith("Runtime:") and last.endswith("Re " + want), last
