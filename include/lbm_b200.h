@@ -165,10 +165,12 @@ int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary strea
 typedef struct {
 	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = default */
 	int block;        /* threads per CTA; 0 = default */
-	int neighbour;    /* 0 = warp shuffle for the +-1 column element, 1 = direct load, 2 = TMA-staged rows */
+	int neighbour;    /* 0 = warp shuffle for the +-1 column element, 1 = direct load */
 	int hints;        /* 0 = default caching, 1 = L1::no_allocate loads + .cs stores */
-	int ctas_per_sm;  /* >0: persistent grid of 148*ctas_per_sm CTAs, 0 = one pass */
-	int use_graph;    /* replay steps from a captured CUDA graph */
+	int ctas_per_sm;  /* >0: cap the grid at SMs*ctas_per_sm CTAs (grid-stride), 0 = one pass */
+	int persistent;   /* 1: all steps of a run in ONE cooperative launch, CTAs ordered by per-CTA
+	                     progress counters instead of kernel boundaries; 0: one launch per step;
+	                     -1 (default): on for lattices up to 16 Mi sites */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);

@@ -42,6 +42,9 @@ int fail(int code, const char *fmt, ...)
 	} while (0)
 
 enum { SYNC_SELF = 0, SYNC_LOCAL = 1, SYNC_FLAGS = 2 };
+enum { PROGRESS_SLOTS = 8192 };
+// lattices up to this many sites step inside the persistent kernel by default (lbm_tuning.persistent = -1)
+const unsigned long long PERSISTENT_AUTO_SITES = 16ull << 20;
 
 struct Peer {
 	real_t *f[2];      // neighbour's buffers A, B (storage row 0)
@@ -76,12 +79,11 @@ struct lbm_ctx {
 	int n_ipc_opened;
 	lbm_tuning tune;
 	long long launches;
+	int launches_persistent;
 	int has_state;
 	real_t w0, w14, w58, itau, a14, a58;
 	double itau_d;
-	// captured CUDA graph of one DoTimeStep-pair in steady state
-	cudaGraphExec_t graph_exec;
-	int graph_steps;
+	int *progress;               // persistent kernel: per-CTA step counters [PROGRESS_SLOTS] + abort word
 };
 
 namespace {
@@ -181,6 +183,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (e == cudaSuccess) e = cudaMalloc(&c->f[1], fbytes);
 	if (e == cudaSuccess) e = cudaMalloc(&c->mask, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMalloc(&c->flags, 4 * sizeof(int));
+	if (e == cudaSuccess) e = cudaMalloc(&c->progress, (PROGRESS_SLOTS + 1) * sizeof(int));
 	if (e == cudaSuccess) e = cudaMemset(c->f[0], 0, fbytes);
 	if (e == cudaSuccess) e = cudaMemset(c->f[1], 0, fbytes);
 	if (e == cudaSuccess) e = cudaMemset(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
@@ -207,7 +210,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	c->tune.neighbour = 0;
 	c->tune.hints = 0;
 	c->tune.ctas_per_sm = 0;
-	c->tune.use_graph = 0;
+	c->tune.persistent = -1;
 	*out = c;
 	return LBM_OK;
 }
@@ -217,7 +220,6 @@ int lbm_destroy(lbm_ctx *c)
 	if (!c) return LBM_OK;
 	cudaSetDevice(c->cfg.device);
 	cudaDeviceSynchronize();
-	if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
 	for (int k = 0; k < c->n_ipc_opened; k++) cudaIpcCloseMemHandle(c->ipc_opened[k]);
 	for (int k = 0; k < 2; k++) {
 		if (c->f[k]) cudaFree(c->f[k]);
@@ -226,6 +228,7 @@ int lbm_destroy(lbm_ctx *c)
 	}
 	if (c->mask) cudaFree(c->mask);
 	if (c->flags) cudaFree(c->flags);
+	if (c->progress) cudaFree(c->progress);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
 	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
 	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -311,6 +314,60 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		c->launches++;
 	}
 	return LBM_OK;
+}
+
+template <int V, int NB>
+int launch_persistent_inst(lbm_ctx *c, const StepParams<real_t> &p, int nsteps, int last_tail, cudaStream_t st)
+{
+	auto kern = stream_collide_persistent_kernel<real_t, V, NB>;
+	const int block = c->tune.block;
+	int occ = 0;
+	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, block, 0));
+	if (c->tune.ctas_per_sm > 0 && occ > c->tune.ctas_per_sm) occ = c->tune.ctas_per_sm;
+	if (occ < 1) return fail(LBM_ERR_CUDA, "persistent kernel does not fit an SM at block %d", block);
+	long long maxgrid = (long long)occ * sm_count(c->cfg.device);
+	if (maxgrid > PROGRESS_SLOTS) maxgrid = PROGRESS_SLOTS;
+	const unsigned long long total = (unsigned long long)c->nxl * (unsigned)(c->nyvec / V);
+	unsigned long long chunk = (total + maxgrid - 1) / maxgrid;
+	chunk = (chunk + 31) / 32 * 32;
+	const unsigned grid = (unsigned)((total + chunk - 1) / chunk);
+	PersistParams q;
+	q.nsteps = nsteps; q.last_tail_source = last_tail; q.chunk = (uint32_t)chunk;
+	q.progress = c->progress; q.abort = c->progress + PROGRESS_SLOTS;
+	q.timeout_ns = 10ull * 1000 * 1000 * 1000;
+	CK(cudaMemsetAsync(c->progress, 0, (PROGRESS_SLOTS + 1) * sizeof(int), st));
+	StepParams<real_t> pp = p;
+	void *args[] = {(void *)&pp, (void *)&q};
+	CK(cudaLaunchCooperativeKernel((const void *)kern, dim3(grid), dim3(block), args, 0, st));
+	c->launches++;
+	c->launches_persistent = 1;
+	return LBM_OK;
+}
+
+// nsteps lattice steps starting from buffer `src` in ONE cooperative launch (single-slab contexts
+// whose rows are all vector columns); tail source on every step but the last unless last_tail
+int launch_persistent(lbm_ctx *c, int src, int nsteps, int last_tail, cudaStream_t st)
+{
+	StepParams<real_t> p = make_params(c, src, 0, c->nxl, 1);
+	int V = c->tune.vec;
+	if (V > c->vw) V = c->vw;
+	const int nb = c->tune.neighbour;
+	switch (V) {
+	case 1: return launch_persistent_inst<1, 1>(c, p, nsteps, last_tail, st);
+	case 2: return nb ? launch_persistent_inst<2, 1>(c, p, nsteps, last_tail, st) : launch_persistent_inst<2, 0>(c, p, nsteps, last_tail, st);
+	case 4: return nb ? launch_persistent_inst<4, 1>(c, p, nsteps, last_tail, st) : launch_persistent_inst<4, 0>(c, p, nsteps, last_tail, st);
+#ifdef LBM_FLOAT
+	case 8: return nb ? launch_persistent_inst<8, 1>(c, p, nsteps, last_tail, st) : launch_persistent_inst<8, 0>(c, p, nsteps, last_tail, st);
+#endif
+	}
+	return fail(LBM_ERR_ARG, "launch_persistent: vec %d", V);
+}
+
+bool use_persistent(const lbm_ctx *c)
+{
+	if (c->sync_mode != SYNC_SELF || c->vw <= 1 || c->nyvec != c->ny) return false;
+	if (c->tune.persistent >= 0) return c->tune.persistent != 0;
+	return (unsigned long long)c->nxl * c->ny <= PERSISTENT_AUTO_SITES;
 }
 
 int launch_source(lbm_ctx *c, int buf, cudaStream_t st)
@@ -524,6 +581,11 @@ int lbm_sync(lbm_ctx *c)
 	if ((rc = set_device(c))) return rc;
 	CK(cudaStreamSynchronize(c->stream[1]));
 	CK(cudaStreamSynchronize(c->stream[0]));
+	if (c->sync_mode == SYNC_SELF && c->launches_persistent) {
+		int ab = 0;
+		CK(cudaMemcpy(&ab, c->progress + PROGRESS_SLOTS, sizeof ab, cudaMemcpyDeviceToHost));
+		if (ab) return fail(LBM_ERR_STATE, "persistent kernel: neighbour wait timed out");
+	}
 	if (c->sync_mode == SYNC_FLAGS) {
 		int fl[4];
 		CK(cudaMemcpy(fl, c->flags, sizeof fl, cudaMemcpyDeviceToHost));
@@ -543,6 +605,7 @@ int lbm_run(lbm_ctx *c, int nsteps)
 	/* Source(A) of the first step; every later Source is fused into the tail of the step
 	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
 	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
+	if (use_persistent(c)) return launch_persistent(c, LBM_BUF_A, nsteps, 0, c->stream[0]);
 	for (int t = 0; t < nsteps; t++)
 		if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
 	return LBM_OK;
@@ -701,6 +764,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.neighbour < 0 || n.neighbour > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: neighbour %d", n.neighbour);
 	if (n.hints < 0 || n.hints > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
 	if (n.ctas_per_sm < 0 || n.ctas_per_sm > 32) return fail(LBM_ERR_ARG, "lbm_set_tuning: ctas_per_sm %d", n.ctas_per_sm);
+	if (n.persistent < -1 || n.persistent > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: persistent %d", n.persistent);
 	c->tune = n;
 	return LBM_OK;
 }

@@ -79,6 +79,7 @@ __device__ __forceinline__ constexpr int opposite(int s) { return s == 0 ? 0 : (
 template <int HINT> __device__ __forceinline__ double ld1(const double *p)
 {
 	if (HINT == 0) return __ldg(p);
+	if (HINT == 2) return __ldcg(p);
 	double v;
 	asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
 	return v;
@@ -86,6 +87,7 @@ template <int HINT> __device__ __forceinline__ double ld1(const double *p)
 template <int HINT> __device__ __forceinline__ float ld1(const float *p)
 {
 	if (HINT == 0) return __ldg(p);
+	if (HINT == 2) return __ldcg(p);
 	float v;
 	asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
 	return v;
@@ -93,16 +95,19 @@ template <int HINT> __device__ __forceinline__ float ld1(const float *p)
 template <int HINT> __device__ __forceinline__ void ld16(const double *p, double &a, double &b)
 {
 	if (HINT == 0) { const double2 t = __ldg(reinterpret_cast<const double2 *>(p)); a = t.x; b = t.y; }
+	else if (HINT == 2) { const double2 t = __ldcg(reinterpret_cast<const double2 *>(p)); a = t.x; b = t.y; }
 	else asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(a), "=d"(b) : "l"(p));
 }
 template <int HINT> __device__ __forceinline__ void ld16(const float *p, float &a, float &b, float &c, float &d)
 {
 	if (HINT == 0) { const float4 t = __ldg(reinterpret_cast<const float4 *>(p)); a = t.x; b = t.y; c = t.z; d = t.w; }
+	else if (HINT == 2) { const float4 t = __ldcg(reinterpret_cast<const float4 *>(p)); a = t.x; b = t.y; c = t.z; d = t.w; }
 	else asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(p));
 }
 template <int HINT> __device__ __forceinline__ void ld8(const float *p, float &a, float &b)
 {
 	if (HINT == 0) { const float2 t = __ldg(reinterpret_cast<const float2 *>(p)); a = t.x; b = t.y; }
+	else if (HINT == 2) { const float2 t = __ldcg(reinterpret_cast<const float2 *>(p)); a = t.x; b = t.y; }
 	else asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "l"(p));
 }
 
@@ -126,11 +131,11 @@ template <int HINT, int V> __device__ __forceinline__ void ldv(const float *p, f
 
 template <int HINT> __device__ __forceinline__ void st1(double *p, double v)
 {
-	if (HINT == 0) *p = v; else __stcs(p, v);
+	if (HINT != 1) *p = v; else __stcs(p, v);
 }
 template <int HINT> __device__ __forceinline__ void st1(float *p, float v)
 {
-	if (HINT == 0) *p = v; else __stcs(p, v);
+	if (HINT != 1) *p = v; else __stcs(p, v);
 }
 template <int HINT, int V> __device__ __forceinline__ void stv(double *p, const double (&v)[V])
 {
@@ -139,7 +144,7 @@ template <int HINT, int V> __device__ __forceinline__ void stv(double *p, const 
 #pragma unroll
 		for (int k = 0; k < V; k += 2) {
 			const double2 t = make_double2(v[k], v[k + 1]);
-			if (HINT == 0) *reinterpret_cast<double2 *>(p + k) = t; else __stcs(reinterpret_cast<double2 *>(p + k), t);
+			if (HINT != 1) *reinterpret_cast<double2 *>(p + k) = t; else __stcs(reinterpret_cast<double2 *>(p + k), t);
 		}
 	}
 }
@@ -148,12 +153,12 @@ template <int HINT, int V> __device__ __forceinline__ void stv(float *p, const f
 	if constexpr (V == 1) st1<HINT>(p, v[0]);
 	else if constexpr (V == 2) {
 		const float2 t = make_float2(v[0], v[1]);
-		if (HINT == 0) *reinterpret_cast<float2 *>(p) = t; else __stcs(reinterpret_cast<float2 *>(p), t);
+		if (HINT != 1) *reinterpret_cast<float2 *>(p) = t; else __stcs(reinterpret_cast<float2 *>(p), t);
 	} else {
 #pragma unroll
 		for (int k = 0; k < V; k += 4) {
 			const float4 t = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
-			if (HINT == 0) *reinterpret_cast<float4 *>(p + k) = t; else __stcs(reinterpret_cast<float4 *>(p + k), t);
+			if (HINT != 1) *reinterpret_cast<float4 *>(p + k) = t; else __stcs(reinterpret_cast<float4 *>(p + k), t);
 		}
 	}
 }
@@ -168,6 +173,14 @@ template <typename T> __device__ __forceinline__ T relax_double(T f, T feq, doub
 {
 	const T d = fp<T>::sub(feq, f);
 	return (T)__dadd_rn((double)f, __dmul_rn(itau_d, (double)d));
+}
+
+// the nine relaxations of a fluid lane inside a mixed group (LB.c:456-464); kept out of line so the
+// common all-fluid path carries no predicated fp64 instructions
+template <typename T> __device__ __noinline__ void relax_double_site(const T (&f)[9], const T (&feq)[9], T (&o)[9], double itau_d)
+{
+#pragma unroll
+	for (int s = 0; s < 9; s++) o[s] = relax_double<T>(f[s], feq[s], itau_d);
 }
 
 // Fluid site, operation order of the SIMD path LB.c:360-451.
@@ -203,10 +216,12 @@ __device__ __forceinline__ void collide_vec_order(const T (&f)[9], T (&o)[9], co
 		q[s] = A::add(T(1), A::add(e[s], A::sub(A::mul(T(0.5), A::mul(e[s], e[s])), usq)));
 	const T r0 = A::mul(p.w0, rho), r14 = A::mul(p.w14, rho), r58 = A::mul(p.w58, rho);   // LB.c:425-433
 #pragma unroll
-	for (int s = 0; s < 9; s++) {
-		const T feq = A::mul(q[s], s == 0 ? r0 : (s <= 4 ? r14 : r58));
-		if (sizeof(T) == 4 && dbl) o[s] = relax_double<T>(f[s], feq, p.itau_d);           // LB.c:456-464
-		else o[s] = A::add(f[s], A::mul(p.itau, A::sub(feq, f[s])));                      // LB.c:442-450
+	for (int s = 0; s < 9; s++) q[s] = A::mul(q[s], s == 0 ? r0 : (s <= 4 ? r14 : r58));
+	if (sizeof(T) == 4 && dbl) {
+		relax_double_site<T>(f, q, o, p.itau_d);                                          // LB.c:456-464 (rare: real branch)
+	} else {
+#pragma unroll
+		for (int s = 0; s < 9; s++) o[s] = A::add(f[s], A::mul(p.itau, A::sub(q[s], f[s])));   // LB.c:442-450
 	}
 }
 
@@ -259,104 +274,104 @@ template <typename T> __device__ __forceinline__ void source_site(T (&o)[9], con
 }
 
 // ---------------------------------------------------------------------------
-// the fused pull kernel (StreamCollideVec, LB.c:307-484, + tail ApplySource + halo push)
-//   V    sites per thread (contiguous in j, V*sizeof(T) <= 32 bytes)
-//   NB   0: +-1 column element from the adjacent lane (shuffle), 1: direct load
-//   HINT 0: default caching, 1: L1::no_allocate loads, .cs stores
-// Launch: 1-D grid, blockDim multiple of 32; grid-stride over (row, vector) pairs.
+// the fused pull update of one V-wide vector of sites (StreamCollideVec, LB.c:307-484,
+// + tail ApplySource + halo push)
+//   V     sites per thread (contiguous in j, V*sizeof(T) <= 32 bytes)
+//   NB    0: +-1 column element from the adjacent lane (shuffle), 1: direct load
+//   HINT  0: default caching, 1: L1::no_allocate loads + .cs stores, 2: L2-coherent (.cg) loads
+//   WRAP  true: rows wrap inside this slab (no halo rows read or written) -- the persistent
+//         multi-step kernel; false: rows i-1/i+1 come from the halo rows, boundary rows push
+// All 32 lanes of a warp must call this together (shuffles); `active` predicates the stores.
 // ---------------------------------------------------------------------------
-template <typename T, int V, int NB, int HINT>
-__global__ void __launch_bounds__(512)
-stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
+template <typename T, int V, int NB, int HINT, bool WRAP>
+__device__ __forceinline__ void update_vector(const StepParams<T> &p, const T *__restrict__ src, T *__restrict__ dst,
+                                              uint32_t nvec, uint32_t g, bool active, uint32_t lane, int tail_source)
 {
-	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
-	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
-	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t stride = gridDim.x * blockDim.x;
+	const uint32_t rr = g / nvec;
+	const uint32_t jv = g - rr * nvec;
+	const int r = p.r0 + (int)rr;                            // owned row; storage row r+1
+	const int j0 = p.jmin + (int)jv * V;
 
-	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {   // warp-uniform trip count
-		const uint32_t g0 = base + threadIdx.x;
-		const bool active = g0 < total;
-		const uint32_t g = active ? g0 : total - 1;          // idle lanes shadow the last vector (loads stay legal)
-		const uint32_t rr = g / nvec;
-		const uint32_t jv = g - rr * nvec;
-		const int r = p.r0 + (int)rr;                        // owned row; storage row r+1
-		const int j0 = p.jmin + (int)jv * V;
+	// wrapped columns of the two out-of-vector neighbours (LB.c:337-338)
+	const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
+	const int jr = j0 + V == p.ny ? 0 : j0 + V;
+	const bool edge_l = (NB == 1) || V == 1 || lane == 0 || jv == 0;
+	const bool edge_r = (NB == 1) || V == 1 || lane == 31 || jv == nvec - 1;
 
-		// wrapped columns of the two out-of-vector neighbours (LB.c:337-338)
-		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
-		const int jr = j0 + V == p.ny ? 0 : j0 + V;
-		const bool edge_l = (NB == 1) || V == 1 || lane == 0 || jv == 0;
-		const bool edge_r = (NB == 1) || V == 1 || lane == 31 || jv == nvec - 1;
-
-		const T *row[3];                                     // rows i-1, i, i+1 of the source (halo rows make the wrap)
-		row[0] = p.src + (size_t)r * p.ldy;
-		row[1] = row[0] + p.ldy;
+	const T *row[3];                                         // rows i-1, i, i+1 of the source
+	row[1] = src + (size_t)(r + 1) * p.ldy;
+	if (WRAP) {                                              // x_d, x_u of LB.c:335-336
+		row[0] = src + (size_t)(r == 0 ? p.nxl : r) * p.ldy;
+		row[2] = src + (size_t)(r == p.nxl - 1 ? 1 : r + 2) * p.ldy;
+	} else {                                                 // halo rows make the wrap / the slab seam
+		row[0] = row[1] - p.ldy;
 		row[2] = row[1] + p.ldy;
+	}
 
-		T f[9][V];
+	T f[9][V];
 #pragma unroll
-		for (int s = 0; s < 9; s++) {
-			const T *base_s = row[pull_di(s) + 1] + (size_t)s * p.plane;
-			if constexpr (V == 1) {
-				const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0;
-				f[s][0] = ld1<HINT>(base_s + jj);
-			} else {
-				T own[V];
-				ldv<HINT, V>(base_s + j0, own);
-				if (pull_dj(s) == 0) {
+	for (int s = 0; s < 9; s++) {
+		const T *base_s = row[pull_di(s) + 1] + (size_t)s * p.plane;
+		if constexpr (V == 1) {
+			const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0;
+			f[s][0] = ld1<HINT>(base_s + jj);
+		} else {
+			T own[V];
+			ldv<HINT, V>(base_s + j0, own);
+			if (pull_dj(s) == 0) {
 #pragma unroll
-					for (int k = 0; k < V; k++) f[s][k] = own[k];
-				} else if (pull_dj(s) < 0) {                 // element k comes from column j0+k-1
-					T nb = T(0);
-					if (NB == 0) nb = __shfl_up_sync(0xffffffffu, own[V - 1], 1);
-					if (edge_l) nb = ld1<HINT>(base_s + jl);
-					f[s][0] = nb;
+				for (int k = 0; k < V; k++) f[s][k] = own[k];
+			} else if (pull_dj(s) < 0) {                     // element k comes from column j0+k-1
+				T nb = T(0);
+				if (NB == 0) nb = __shfl_up_sync(0xffffffffu, own[V - 1], 1);
+				if (edge_l) nb = ld1<HINT>(base_s + jl);
+				f[s][0] = nb;
 #pragma unroll
-					for (int k = 1; k < V; k++) f[s][k] = own[k - 1];
-				} else {                                     // element k comes from column j0+k+1
-					T nb = T(0);
-					if (NB == 0) nb = __shfl_down_sync(0xffffffffu, own[0], 1);
-					if (edge_r) nb = ld1<HINT>(base_s + jr);
-					f[s][V - 1] = nb;
+				for (int k = 1; k < V; k++) f[s][k] = own[k - 1];
+			} else {                                         // element k comes from column j0+k+1
+				T nb = T(0);
+				if (NB == 0) nb = __shfl_down_sync(0xffffffffu, own[0], 1);
+				if (edge_r) nb = ld1<HINT>(base_s + jr);
+				f[s][V - 1] = nb;
 #pragma unroll
-					for (int k = 0; k < V - 1; k++) f[s][k] = own[k + 1];
-				}
+				for (int k = 0; k < V - 1; k++) f[s][k] = own[k + 1];
 			}
 		}
+	}
 
-		// wall bits of my V sites and of my aligned VECWIDTH group (LB.c:437-440)
-		const uint32_t word = __ldg(p.mask + (size_t)r * p.ldw + (j0 >> 5));
-		const uint32_t sh = (uint32_t)j0 & 31u;
-		const uint32_t bits = (word >> sh) & ((1u << V) - 1u);
-		bool dbl = false;
-		if (sizeof(T) == 4) dbl = ((word >> (sh & ~(uint32_t)(p.vw - 1))) & ((1u << p.vw) - 1u)) != 0u;
+	// wall bits of my V sites and of my aligned VECWIDTH group (LB.c:437-440)
+	const uint32_t word = __ldg(p.mask + (size_t)r * p.ldw + (j0 >> 5));
+	const uint32_t sh = (uint32_t)j0 & 31u;
+	const uint32_t bits = (word >> sh) & ((1u << V) - 1u);
+	bool dbl = false;
+	if (sizeof(T) == 4) dbl = ((word >> (sh & ~(uint32_t)(p.vw - 1))) & ((1u << p.vw) - 1u)) != 0u;
 
-		T o[9][V];
+	T o[9][V];
 #pragma unroll
-		for (int k = 0; k < V; k++) {
-			T fk[9], ok[9];
+	for (int k = 0; k < V; k++) {
+		T fk[9], ok[9];
 #pragma unroll
-			for (int s = 0; s < 9; s++) fk[s] = f[s][k];
-			if ((bits >> k) & 1u) {
-				bounce<T>(fk, ok);
-			} else {
-				collide_vec_order<T>(fk, ok, p, dbl);
-				if (k == 0 && j0 == 0 && p.tail_source) source_site<T>(ok, p);
-			}
-#pragma unroll
-			for (int s = 0; s < 9; s++) o[s][k] = ok[s];
+		for (int s = 0; s < 9; s++) fk[s] = f[s][k];
+		if ((bits >> k) & 1u) {
+			bounce<T>(fk, ok);
+		} else {
+			collide_vec_order<T>(fk, ok, p, dbl);
+			if (k == 0 && j0 == 0 && tail_source) source_site<T>(ok, p);
 		}
+#pragma unroll
+		for (int s = 0; s < 9; s++) o[s][k] = ok[s];
+	}
 
-		if (active) {
-			T *d = p.dst + (size_t)(r + 1) * p.ldy + j0;
-			if (bits == 0u) stv<HINT, V>(d, o[0]);
-			else {
+	if (active) {
+		T *d = dst + (size_t)(r + 1) * p.ldy + j0;
+		if (bits == 0u) stv<HINT, V>(d, o[0]);
+		else {
 #pragma unroll
-				for (int k = 0; k < V; k++) if (!((bits >> k) & 1u)) d[k] = o[0][k];     // f0 untouched at walls
-			}
+			for (int k = 0; k < V; k++) if (!((bits >> k) & 1u)) d[k] = o[0][k];     // f0 untouched at walls
+		}
 #pragma unroll
-			for (int s = 1; s < 9; s++) stv<HINT, V>(d + (size_t)s * p.plane, o[s]);
+		for (int s = 1; s < 9; s++) stv<HINT, V>(d + (size_t)s * p.plane, o[s]);
+		if (!WRAP) {
 			if (r == 0) {                                    // what the slab below pulls from its row "hi" (LB.c:239,242,243)
 				stv<HINT, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
 				stv<HINT, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
@@ -368,6 +383,116 @@ stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 				stv<HINT, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
 			}
 		}
+	}
+}
+
+// One lattice step per launch.  1-D grid, blockDim multiple of 32; grid-stride over (row, vector) pairs.
+template <typename T, int V, int NB, int HINT>
+__global__ void __launch_bounds__(512)
+stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
+{
+	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
+	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {   // warp-uniform trip count
+		const uint32_t g0 = base + threadIdx.x;
+		const bool active = g0 < total;
+		const uint32_t g = active ? g0 : total - 1;          // idle lanes shadow the last vector (loads stay legal)
+		update_vector<T, V, NB, HINT, false>(p, p.src, p.dst, nvec, g, active, lane, p.tail_source);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Persistent multi-step kernel for lattices whose step is short (tens of microseconds): ONE
+// cooperative launch runs `nsteps` lattice steps.  Each CTA owns a fixed contiguous range of the
+// flattened (row, vector) space; instead of a grid-wide barrier per step, a CTA starts step t as
+// soon as the CTAs owning the rows above/below its range have finished step t-1 (their progress
+// counters, polled with acquire loads) -- the D2Q9 pull only reaches one row and one column away
+// (LB.c:235-243), and the same condition covers the write-after-read hazard of the A/B buffers.
+// No launch gaps, no per-step ramp-up/drain.  Source data is read with .cg (L2-coherent) loads:
+// L1 is not coherent across CTAs and the same addresses are rewritten every second step.
+// ---------------------------------------------------------------------------
+struct PersistParams {
+	int nsteps;
+	int last_tail_source;       // tail_source of the last step (0: leave A un-sourced, LB.c:192-205)
+	uint32_t chunk;             // vectors per CTA (multiple of 32)
+	int *progress;              // [gridDim.x] completed steps per CTA, zeroed before launch
+	int *abort;                 // set when a wait timed out
+	unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ int ld_acquire_gpu(const int *p)
+{
+	int v;
+	asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_release_gpu(int *p, int v)
+{
+	asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <typename T, int V, int NB>
+__global__ void __launch_bounds__(512)
+stream_collide_persistent_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ PersistParams q)
+{
+	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
+	const uint32_t total = (uint32_t)p.nxl * nvec;           // r0 == 0, r1 == nxl
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t lo = blockIdx.x * q.chunk;
+	const uint32_t hi = min(lo + q.chunk, total);
+	__shared__ int s_abort;
+	if (threadIdx.x == 0) s_abort = 0;
+
+	// CTAs whose ranges touch [lo - 2*nvec, hi + 2*nvec] (periodic in the flattened index): one row up
+	// and down, plus the y-wrap of the diagonal pulls at j = 0 and j = ny-1 (e.g. f8 of (r, 0) comes
+	// from (r+1, ny-1) = g + 2*nvec - 1).  Up to three index intervals, thread k < 3 polls interval k.
+	long long a0 = (long long)lo - 2ll * nvec, b0 = (long long)hi + 2ll * nvec;
+	uint32_t ia = 0, ib = 0;
+	bool poll = false;
+	if ((unsigned long long)(b0 - a0 + 1) >= total) {        // tiny lattice: depend on everybody
+		if (threadIdx.x == 0) { ia = 0; ib = gridDim.x - 1; poll = true; }
+	} else if (threadIdx.x == 0) {
+		ia = (uint32_t)max(a0, 0ll) / q.chunk; ib = (uint32_t)min(b0, (long long)total - 1) / q.chunk; poll = true;
+	} else if (threadIdx.x == 1 && a0 < 0) {
+		ia = (uint32_t)(a0 + total) / q.chunk; ib = (total - 1) / q.chunk; poll = true;
+	} else if (threadIdx.x == 2 && b0 >= (long long)total) {
+		ia = 0; ib = (uint32_t)(b0 - total) / q.chunk; poll = true;
+	}
+	__syncthreads();
+
+	const T *src = p.src;
+	T *dst = p.dst;
+	for (int t = 0; t < q.nsteps; t++) {
+		if (t > 0) {
+			if (poll) {
+				unsigned long long t0 = 0;
+				for (uint32_t c = ia; c <= ib; c++) {
+					while (ld_acquire_gpu(q.progress + c) < t) {
+						if (t0 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+						unsigned long long now;
+						asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+						if (now - t0 > q.timeout_ns || ld_acquire_gpu(q.abort)) { *q.abort = 1; s_abort = 1; break; }
+					}
+				}
+			}
+			__syncthreads();
+			if (s_abort) return;
+		}
+		const int tail = (t == q.nsteps - 1) ? q.last_tail_source : 1;
+		for (uint32_t base = lo; base < hi; base += blockDim.x) {                    // warp-uniform trip count
+			const uint32_t g0 = base + threadIdx.x;
+			const bool active = g0 < hi;
+			const uint32_t g = active ? g0 : hi - 1;
+			update_vector<T, V, NB, 2, true>(p, src, dst, nvec, g, active, lane, tail);
+		}
+		__syncthreads();                                     // all of this CTA's stores issued ...
+		if (threadIdx.x == 0) {
+			__threadfence();                                 // ... and visible device-wide before the counter moves
+			st_release_gpu(q.progress + blockIdx.x, t + 1);
+		}
+		const T *tmp = src; src = dst; dst = const_cast<T *>(tmp);
 	}
 }
 
