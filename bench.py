@@ -167,14 +167,26 @@ def timed_jobs(lat, timesteps, warmup, steps, reinit):
     return ms, launches
 
 
-def roofline(prec, sites_per_launch, step_launches, total_ms, peak, peak_src):
-    per_launch_s = total_ms * 1e-3 / step_launches
-    achieved = BYTES_PER_UPDATE[prec] * sites_per_launch / per_launch_s / 1e9
-    return {"bound": "hbm", "kernel": "lbm::stream_collide_vec_kernel", "achieved": round(achieved, 1), "peak": peak,
-            "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": ncu_traffic(prec),
-            "algorithmic_bytes_per_launch": BYTES_PER_UPDATE[prec] * sites_per_launch,
-            "avg_launch_us": round(per_launch_s * 1e6, 3), "peak_source": peak_src,
-            "frac_of_nominal_8TBs": round(achieved / 8000.0, 4)}
+def roofline(prec, sites, timesteps_total, kernel_launches, total_ms, peak, peak_src):
+    """Dominant kernel = the fused stream-collide step.  `kernel_launches` launches covered
+    `timesteps_total` lattice steps in `total_ms` of device time (persistent kernel: one launch per job)."""
+    per_launch_s = total_ms * 1e-3 / kernel_launches
+    bytes_per_launch = BYTES_PER_UPDATE[prec] * sites * (timesteps_total // kernel_launches)
+    achieved = bytes_per_launch / per_launch_s / 1e9
+    persistent = kernel_launches < timesteps_total
+    return {"bound": "hbm", "kernel": "lbm::stream_collide_persistent_kernel" if persistent else "lbm::stream_collide_vec_kernel",
+            "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+            "traffic": ncu_traffic(prec), "algorithmic_bytes_per_launch": bytes_per_launch,
+            "timesteps_per_launch": timesteps_total // kernel_launches,
+            "avg_launch_us": round(per_launch_s * 1e6, 3), "us_per_timestep": round(total_ms * 1e3 / timesteps_total, 3),
+            "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4)}
+
+
+def step_kernel_launches(launches, jobs, timesteps):
+    """launches of the step kernel among `launches` counted over `jobs` lbm_run calls: each call adds
+    ApplySource + halo refresh (2) and either `timesteps` step launches or one persistent launch."""
+    per_job = launches // jobs - 2
+    return jobs * (timesteps if per_job >= timesteps else 1)
 
 
 def bench_single(args):
@@ -201,7 +213,7 @@ def bench_single(args):
             total_ms = sum(ms)
             mlups = nx * ny * T * args.steps / (total_ms * 1e-3) / 1e6
             res = {"value": round(mlups, 1), "ms_per_step": round(total_ms / args.steps, 3), "launches": launches,
-                   "roofline": roofline(prec, nx * ny, T * args.steps, total_ms, peak, peak_src),
+                   "roofline": roofline(prec, nx * ny, T * args.steps, step_kernel_launches(launches, args.steps, T), total_ms, peak, peak_src),
                    "ms_min": round(min(ms), 3), "ms_max": round(max(ms), 3), "tuning": lat.get_tuning()}
 
             # e2e: host buffers (pinned) -> lbm_upload -> lbm_run -> lbm_download, wall clock
@@ -314,7 +326,7 @@ def bench_multi(args):
         mlups = nx * ny * T * args.steps / (total_ms * 1e-3) / 1e6
         res = {"value": round(mlups, 1), "ms_per_step": round(total_ms / args.steps, 3), "launches": launches,
                "wall_ms_per_step": round(1e3 * wall / args.steps, 3),
-               "roofline": roofline(prec, WEAK["nx_per_gpu"] * ny, T * args.steps, total_ms, peak, peak_src)}
+               "roofline": roofline(prec, WEAK["nx_per_gpu"] * ny, T * args.steps, T * args.steps, total_ms, peak, peak_src)}
         res["reynolds"] = dl.gather_reynolds()
 
         # e2e: every rank uploads its slab from host memory, runs, downloads it again

@@ -175,14 +175,6 @@ template <typename T> __device__ __forceinline__ T relax_double(T f, T feq, doub
 	return (T)__dadd_rn((double)f, __dmul_rn(itau_d, (double)d));
 }
 
-// the nine relaxations of a fluid lane inside a mixed group (LB.c:456-464); kept out of line so the
-// common all-fluid path carries no predicated fp64 instructions
-template <typename T> __device__ __noinline__ void relax_double_site(const T (&f)[9], const T (&feq)[9], T (&o)[9], double itau_d)
-{
-#pragma unroll
-	for (int s = 0; s < 9; s++) o[s] = relax_double<T>(f[s], feq[s], itau_d);
-}
-
 // Fluid site, operation order of the SIMD path LB.c:360-451.
 // dbl != 0 selects the mixed-group fallback LB.c:455-465 (identical bits in DP).
 template <typename T>
@@ -217,11 +209,13 @@ __device__ __forceinline__ void collide_vec_order(const T (&f)[9], T (&o)[9], co
 	const T r0 = A::mul(p.w0, rho), r14 = A::mul(p.w14, rho), r58 = A::mul(p.w58, rho);   // LB.c:425-433
 #pragma unroll
 	for (int s = 0; s < 9; s++) q[s] = A::mul(q[s], s == 0 ? r0 : (s <= 4 ? r14 : r58));
-	if (sizeof(T) == 4 && dbl) {
-		relax_double_site<T>(f, q, o, p.itau_d);                                          // LB.c:456-464 (rare: real branch)
-	} else {
+	// Mixed group (LB.c:455-465): fluid lanes relax with 1/tau in double; only SP can tell the
+	// difference.  (Measured alternative: a warp-uniform branch around the fp64 code costs 14 more
+	// registers than letting ptxas predicate these few instructions off -- kept predicated.)
 #pragma unroll
-		for (int s = 0; s < 9; s++) o[s] = A::add(f[s], A::mul(p.itau, A::sub(q[s], f[s])));   // LB.c:442-450
+	for (int s = 0; s < 9; s++) {
+		if (sizeof(T) == 4 && dbl) o[s] = relax_double<T>(f[s], q[s], p.itau_d);              // LB.c:456-464
+		else o[s] = A::add(f[s], A::mul(p.itau, A::sub(q[s], f[s])));                         // LB.c:442-450
 	}
 }
 

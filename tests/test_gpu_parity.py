@@ -46,11 +46,15 @@ def _assert_same(got, want, what):
 # ---------------------------------------------------------------------------------------------
 # against the golden vectors of the compiled reference (every case, incl. 10,000 steps)
 # ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("persistent", [-1, 0, 1], ids=["auto", "per-step-launch", "persistent"])
 @pytest.mark.parametrize("name", list(cases.CASES))
-def test_cuda_matches_reference_golden(name):
+def test_cuda_matches_reference_golden(name, persistent):
     c, g = cases.CASES[name], GOLDEN[name]
+    if persistent == 0 and c["steps"] > 1000:
+        pytest.skip("10,000-step cases run once per engine")
     fA, walls = cases.make_inputs(name)
     with _lattice(c) as lat:
+        lat.set_tuning(persistent=persistent)
         lat.upload(fA, walls)
         lat.run(c["steps"])
         a, b = lat.download("A"), lat.download("B")
@@ -83,11 +87,13 @@ def test_cuda_matches_oracle_shapes(prec, isa, shape):
         walls[:] = 0                           # no channel rows when the lattice is 1-2 rows high
         walls[0, ::5] = 1
     o = _oracle(c, fA, walls, c["steps"])
-    with _lattice(c) as lat:
-        lat.upload(fA, walls)
-        lat.run(c["steps"])
-        _assert_same(lat.download("A"), o.f_view("A"), "fA")
-        _assert_same(lat.download("B"), o.f_view("B"), "fB")
+    for persistent in (0, 1):
+        with _lattice(c) as lat:
+            lat.set_tuning(persistent=persistent)
+            lat.upload(fA, walls)
+            lat.run(c["steps"])
+            _assert_same(lat.download("A"), o.f_view("A"), f"fA persistent={persistent}")
+            _assert_same(lat.download("B"), o.f_view("B"), f"fB persistent={persistent}")
 
 
 def _variants(prec):
@@ -96,10 +102,13 @@ def _variants(prec):
     for v in vecs:
         for nb in (0, 1):
             for hints in (0, 1):
-                out.append(dict(vec=v, neighbour=nb, hints=hints, block=256, ctas_per_sm=0))
-    out += [dict(vec=vecs[-1], neighbour=0, hints=0, block=128, ctas_per_sm=2),
-            dict(vec=2, neighbour=0, hints=1, block=512, ctas_per_sm=1),
-            dict(vec=2, neighbour=0, hints=0, block=64, ctas_per_sm=8)]
+                out.append(dict(vec=v, neighbour=nb, hints=hints, block=256, ctas_per_sm=0, persistent=0))
+            out.append(dict(vec=v, neighbour=nb, hints=0, block=128, ctas_per_sm=0, persistent=1))
+    out += [dict(vec=vecs[-1], neighbour=0, hints=0, block=128, ctas_per_sm=2, persistent=0),
+            dict(vec=2, neighbour=0, hints=1, block=512, ctas_per_sm=1, persistent=0),
+            dict(vec=2, neighbour=0, hints=0, block=64, ctas_per_sm=8, persistent=0),
+            dict(vec=2, neighbour=0, hints=0, block=512, ctas_per_sm=1, persistent=1),
+            dict(vec=vecs[-1], neighbour=1, hints=0, block=64, ctas_per_sm=3, persistent=1)]
     return out
 
 

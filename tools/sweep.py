@@ -29,15 +29,18 @@ def main():
             with Lattice(nx, ny, prec) as lat:
                 lat.InitializeArrays(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=nx // 10)
                 lat.run_timed(T)
-                combos = itertools.product(vecs, (0, 1), (0, 1), (128, 256, 512), (0, 4, 8))
-                for vec, nb, hints, block, ctas in combos:
+                combos = list(itertools.product(vecs, (0, 1), (0, 1), (128, 256), (0,), (0,)))
+                combos += list(itertools.product(vecs, (0, 1), (0,), (128, 256, 512), (0, 1, 2, 3, 4, 6, 8), (1,)))
+                for vec, nb, hints, block, ctas, pers in combos:
                     if quick and (block != 256 or ctas not in (0,)):
                         continue
-                    lat.set_tuning(vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas)
+                    if pers and vec == 1 and nb == 0:
+                        continue                     # vec 1 has no shuffle variant
+                    lat.set_tuning(vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas, persistent=pers)
                     lat.run_timed(max(2, T // 10))
                     ms = min(lat.run_timed(T) for _ in range(2))
                     mlups = nx * ny * T / (ms * 1e-3) / 1e6
-                    rec = dict(prec=prec, nx=nx, ny=ny, T=T, vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas,
+                    rec = dict(prec=prec, nx=nx, ny=ny, T=T, vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas, persistent=pers,
                                ms=round(ms, 3), mlups=round(mlups, 1), gbs=round(mlups * BYTES[prec] / 1e3, 1),
                                frac=round(mlups * BYTES[prec] / 1e3 / peak, 4))
                     out.append(rec)
@@ -46,10 +49,11 @@ def main():
     json.dump(out, open(os.path.join(ROOT, "gpurun_out", "sweep.json"), "w"), indent=0)
     for prec in ("dp", "sp"):
         for nx, ny, _ in lattices:
-            best = sorted((r for r in out if r["prec"] == prec and r["nx"] == nx), key=lambda r: -r["mlups"])[:5]
-            print(f"== best {prec} {nx}x{ny}")
-            for r in best:
-                print("  ", {k: r[k] for k in ("vec", "neighbour", "hints", "block", "ctas_per_sm", "mlups", "gbs", "frac")})
+            for pers in (0, 1):
+              best = sorted((r for r in out if r["prec"] == prec and r["nx"] == nx and r["persistent"] == pers), key=lambda r: -r["mlups"])[:4]
+              print(f"== best {prec} {nx}x{ny} persistent={pers}")
+              for r in best:
+                print("  ", {k: r[k] for k in ("persistent", "vec", "neighbour", "hints", "block", "ctas_per_sm", "mlups", "gbs", "frac")})
 
 
 if __name__ == "__main__":
