@@ -163,14 +163,16 @@ int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary strea
 
 /* ---- tuning / accounting ---- */
 typedef struct {
-	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = default */
+	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = by lattice size (DP: 1 up to 16 Mi sites, else 4; SP: 4) */
 	int block;        /* threads per CTA; 0 = default */
 	int neighbour;    /* 0 = warp shuffle for the +-1 column element, 1 = direct load */
 	int hints;        /* 0 = default caching, 1 = L1::no_allocate loads + .cs stores */
 	int ctas_per_sm;  /* >0: cap the grid at SMs*ctas_per_sm CTAs (grid-stride), 0 = one pass */
 	int persistent;   /* 1: all steps of a run in ONE cooperative launch, CTAs ordered by per-CTA
-	                     progress counters instead of kernel boundaries; 0: one launch per step;
-	                     -1 (default): on for lattices up to 16 Mi sites */
+	                     progress counters instead of kernel boundaries; 0 (default): one launch per step */
+	int pdl;          /* 1: step kernels are launched with programmatic dependent launch, so the next
+	                     step's CTAs are resident (waiting in griddepcontrol.wait) while this one drains */
+	int graph;        /* >0: steps are replayed from a captured CUDA graph of `graph` step pairs */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);

@@ -43,8 +43,7 @@ int fail(int code, const char *fmt, ...)
 
 enum { SYNC_SELF = 0, SYNC_LOCAL = 1, SYNC_FLAGS = 2 };
 enum { PROGRESS_SLOTS = 8192 };
-// lattices up to this many sites step inside the persistent kernel by default (lbm_tuning.persistent = -1)
-const unsigned long long PERSISTENT_AUTO_SITES = 16ull << 20;
+
 
 struct Peer {
 	real_t *f[2];      // neighbour's buffers A, B (storage row 0)
@@ -84,9 +83,29 @@ struct lbm_ctx {
 	real_t w0, w14, w58, itau, a14, a58;
 	double itau_d;
 	int *progress;               // persistent kernel: per-CTA step counters [PROGRESS_SLOTS] + abort word
+	cudaGraphExec_t graph_exec;  // captured `graph_pairs` x (A->B, B->A) steps with the current tuning
+	int graph_pairs;
 };
 
 namespace {
+
+int default_vec(const lbm_ctx *c)
+{
+	if (sizeof(real_t) == 4) return 4;
+	return (unsigned long long)c->nxl * c->ny <= (16ull << 20) ? 1 : 4;
+}
+
+int default_small_dp(const lbm_ctx *c)
+{
+	return sizeof(real_t) == 8 && (unsigned long long)c->nxl * c->ny <= (16ull << 20);
+}
+
+void drop_graph(lbm_ctx *c)
+{
+	if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
+	c->graph_exec = nullptr;
+	c->graph_pairs = 0;
+}
 
 int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_OK; }
 
@@ -205,12 +224,17 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	c->up.nxl = c->dn.nxl = c->nxl;
 	c->sync_mode = SYNC_SELF;
 
-	c->tune.vec = sizeof(real_t) == 8 ? 2 : 4;
-	c->tune.block = 256;
-	c->tune.neighbour = 0;
+	/* measured best on B200 at every size (profiles/r01_run2): direct neighbour loads, 128-thread CTAs */
+	c->tune.vec = default_vec(c);
+	c->tune.block = 128;
+	c->tune.neighbour = 1;
 	c->tune.hints = 0;
 	c->tune.ctas_per_sm = 0;
-	c->tune.persistent = -1;
+	c->tune.persistent = 0;
+	/* small DP lattices are launch-bound (a step is ~35 us): PDL + graph replay of 10 step pairs measured
+	 * 43.7 vs 41.1 GLUPS at 400x4000 (profiles/r01_run3); no gain for SP or for large lattices */
+	c->tune.pdl = default_small_dp(c);
+	c->tune.graph = default_small_dp(c) ? 10 : 0;
 	*out = c;
 	return LBM_OK;
 }
@@ -227,6 +251,7 @@ int lbm_destroy(lbm_ctx *c)
 		if (c->ev_bnd[k]) cudaEventDestroy(c->ev_bnd[k]);
 	}
 	if (c->mask) cudaFree(c->mask);
+	drop_graph(c);
 	if (c->flags) cudaFree(c->flags);
 	if (c->progress) cudaFree(c->progress);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
@@ -244,19 +269,28 @@ int lbm_destroy(lbm_ctx *c)
 namespace {
 
 template <int V, int NB, int HINT>
-cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st)
+cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
 {
-	stream_collide_vec_kernel<real_t, V, NB, HINT><<<grid, block, 0, st>>>(p);
-	return cudaGetLastError();
+	if (!pdl) {
+		stream_collide_vec_kernel<real_t, V, NB, HINT><<<grid, block, 0, st>>>(p);
+		return cudaGetLastError();
+	}
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+	cudaLaunchAttribute at[1];
+	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	at[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = at; cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, stream_collide_vec_kernel<real_t, V, NB, HINT>, p);
 }
 
 template <int V>
-cudaError_t launch_vec_v(int nb, int hint, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st)
+cudaError_t launch_vec_v(int nb, int hint, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
 {
-	if (nb == 0 && hint == 0) return launch_vec_inst<V, 0, 0>(p, grid, block, st);
-	if (nb == 0 && hint == 1) return launch_vec_inst<V, 0, 1>(p, grid, block, st);
-	if (nb == 1 && hint == 0) return launch_vec_inst<V, 1, 0>(p, grid, block, st);
-	return launch_vec_inst<V, 1, 1>(p, grid, block, st);
+	if (nb == 0 && hint == 0) return launch_vec_inst<V, 0, 0>(p, grid, block, st, pdl);
+	if (nb == 0 && hint == 1) return launch_vec_inst<V, 0, 1>(p, grid, block, st, pdl);
+	if (nb == 1 && hint == 0) return launch_vec_inst<V, 1, 0>(p, grid, block, st, pdl);
+	return launch_vec_inst<V, 1, 1>(p, grid, block, st, pdl);
 }
 
 int sm_count(int device)
@@ -287,13 +321,15 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			const unsigned long long cap = (unsigned long long)sm_count(c->cfg.device) * c->tune.ctas_per_sm;
 			if (grid > cap) grid = cap;
 		}
+		/* PDL only where consecutive step kernels follow each other on one stream with nothing between */
+		const int pdl = c->tune.pdl && c->sync_mode == SYNC_SELF && c->nyvec == c->ny;
 		cudaError_t e;
 		switch (V) {
-		case 1: e = launch_vec_v<1>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
-		case 2: e = launch_vec_v<2>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
-		case 4: e = launch_vec_v<4>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
+		case 1: e = launch_vec_v<1>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
+		case 2: e = launch_vec_v<2>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
+		case 4: e = launch_vec_v<4>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
 #ifdef LBM_FLOAT
-		case 8: e = launch_vec_v<8>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st); break;
+		case 8: e = launch_vec_v<8>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
 #endif
 		default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 		}
@@ -366,8 +402,7 @@ int launch_persistent(lbm_ctx *c, int src, int nsteps, int last_tail, cudaStream
 bool use_persistent(const lbm_ctx *c)
 {
 	if (c->sync_mode != SYNC_SELF || c->vw <= 1 || c->nyvec != c->ny) return false;
-	if (c->tune.persistent >= 0) return c->tune.persistent != 0;
-	return (unsigned long long)c->nxl * c->ny <= PERSISTENT_AUTO_SITES;
+	return c->tune.persistent != 0;
 }
 
 int launch_source(lbm_ctx *c, int buf, cudaStream_t st)
@@ -606,7 +641,36 @@ int lbm_run(lbm_ctx *c, int nsteps)
 	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
 	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
 	if (use_persistent(c)) return launch_persistent(c, LBM_BUF_A, nsteps, 0, c->stream[0]);
-	for (int t = 0; t < nsteps; t++)
+	int t = 0;
+	if (c->tune.graph > 0 && c->sync_mode == SYNC_SELF) {
+		/* replay whole (A->B, B->A) pairs, all with the tail source, from a captured graph; the last
+		 * pair (whose final step must leave A un-sourced) is launched directly below */
+		const int pairs = c->tune.graph;
+		if (nsteps - 2 >= 2 * pairs) {
+			if (!c->graph_exec || c->graph_pairs != pairs) {
+				drop_graph(c);
+				cudaGraph_t g = nullptr;
+				CK(cudaStreamBeginCapture(c->stream[0], cudaStreamCaptureModeThreadLocal));
+				rc = LBM_OK;
+				const long long l0 = c->launches;
+				for (int k = 0; k < 2 * pairs && rc == LBM_OK; k++) rc = enqueue_step(c, k & 1, 1);
+				c->launches = l0;                               /* captured, not launched */
+				cudaError_t e = cudaStreamEndCapture(c->stream[0], &g);
+				if (rc != LBM_OK) { if (g) cudaGraphDestroy(g); return rc; }
+				CK(e);
+				e = cudaGraphInstantiate(&c->graph_exec, g, 0);
+				cudaGraphDestroy(g);
+				CK(e);
+				c->graph_pairs = pairs;
+			}
+			const int per_graph = (c->nyvec == c->ny || c->vw == 1) ? 1 : 2;   /* kernels per step */
+			for (; nsteps - 2 - t >= 2 * pairs; t += 2 * pairs) {
+				CK(cudaGraphLaunch(c->graph_exec, c->stream[0]));
+				c->launches += (long long)2 * pairs * per_graph;
+			}
+		}
+	}
+	for (; t < nsteps; t++)
 		if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
 	return LBM_OK;
 }
@@ -756,15 +820,18 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 {
 	if (!c || !t) return fail(LBM_ERR_ARG, "lbm_set_tuning: null argument");
 	lbm_tuning n = *t;
-	if (n.vec == 0) n.vec = sizeof(real_t) == 8 ? 2 : 4;
-	if (n.block == 0) n.block = 256;
+	if (n.vec == 0) n.vec = default_vec(c);
+	if (n.block == 0) n.block = 128;
 	const int vmax = 32 / (int)sizeof(real_t);
 	if ((n.vec != 1 && n.vec != 2 && n.vec != 4 && n.vec != 8) || n.vec > vmax) return fail(LBM_ERR_ARG, "lbm_set_tuning: vec %d", n.vec);
 	if (n.block < 32 || n.block > 512 || (n.block & 31)) return fail(LBM_ERR_ARG, "lbm_set_tuning: block %d", n.block);
 	if (n.neighbour < 0 || n.neighbour > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: neighbour %d", n.neighbour);
 	if (n.hints < 0 || n.hints > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
 	if (n.ctas_per_sm < 0 || n.ctas_per_sm > 32) return fail(LBM_ERR_ARG, "lbm_set_tuning: ctas_per_sm %d", n.ctas_per_sm);
-	if (n.persistent < -1 || n.persistent > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: persistent %d", n.persistent);
+	if (n.persistent < 0 || n.persistent > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: persistent %d", n.persistent);
+	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
+	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
+	drop_graph(c);
 	c->tune = n;
 	return LBM_OK;
 }

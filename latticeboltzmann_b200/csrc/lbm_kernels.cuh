@@ -385,10 +385,14 @@ template <typename T, int V, int NB, int HINT>
 __global__ void __launch_bounds__(512)
 stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 {
+	// Programmatic dependent launch (no-ops unless launched with the PDL attribute): let the NEXT step's
+	// CTAs become resident while this step drains, and do not touch f before the PREVIOUS step is complete.
+	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
 	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t stride = gridDim.x * blockDim.x;
+	asm volatile("griddepcontrol.wait;" ::: "memory");
 	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {   // warp-uniform trip count
 		const uint32_t g0 = base + threadIdx.x;
 		const bool active = g0 < total;
@@ -436,23 +440,25 @@ stream_collide_persistent_kernel(const __grid_constant__ StepParams<T> p, const 
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t lo = blockIdx.x * q.chunk;
 	const uint32_t hi = min(lo + q.chunk, total);
-	__shared__ int s_abort;
-	if (threadIdx.x == 0) s_abort = 0;
+	__shared__ int s_abort, s_ndeps;
+	__shared__ uint32_t s_dep0[3], s_depn[3];
 
 	// CTAs whose ranges touch [lo - 2*nvec, hi + 2*nvec] (periodic in the flattened index): one row up
 	// and down, plus the y-wrap of the diagonal pulls at j = 0 and j = ny-1 (e.g. f8 of (r, 0) comes
-	// from (r+1, ny-1) = g + 2*nvec - 1).  Up to three index intervals, thread k < 3 polls interval k.
-	long long a0 = (long long)lo - 2ll * nvec, b0 = (long long)hi + 2ll * nvec;
-	uint32_t ia = 0, ib = 0;
-	bool poll = false;
-	if ((unsigned long long)(b0 - a0 + 1) >= total) {        // tiny lattice: depend on everybody
-		if (threadIdx.x == 0) { ia = 0; ib = gridDim.x - 1; poll = true; }
-	} else if (threadIdx.x == 0) {
-		ia = (uint32_t)max(a0, 0ll) / q.chunk; ib = (uint32_t)min(b0, (long long)total - 1) / q.chunk; poll = true;
-	} else if (threadIdx.x == 1 && a0 < 0) {
-		ia = (uint32_t)(a0 + total) / q.chunk; ib = (total - 1) / q.chunk; poll = true;
-	} else if (threadIdx.x == 2 && b0 >= (long long)total) {
-		ia = 0; ib = (uint32_t)(b0 - total) / q.chunk; poll = true;
+	// from (r+1, ny-1) = g + 2*nvec - 1).  Up to three runs of consecutive CTA ids.
+	if (threadIdx.x == 0) {
+		s_abort = 0;
+		const long long a0 = (long long)lo - 2ll * nvec, b0 = (long long)hi + 2ll * nvec;
+		int n = 0;
+		if ((unsigned long long)(b0 - a0 + 1) >= total) {    // tiny lattice: depend on everybody
+			s_dep0[0] = 0; s_depn[0] = gridDim.x; n = 1;
+		} else {
+			const uint32_t ia = (uint32_t)max(a0, 0ll) / q.chunk, ib = (uint32_t)min(b0, (long long)total - 1) / q.chunk;
+			s_dep0[n] = ia; s_depn[n] = ib - ia + 1; n++;
+			if (a0 < 0) { const uint32_t ja = (uint32_t)(a0 + total) / q.chunk, jb = (total - 1) / q.chunk; s_dep0[n] = ja; s_depn[n] = jb - ja + 1; n++; }
+			if (b0 >= (long long)total) { const uint32_t jb = (uint32_t)(b0 - total) / q.chunk; s_dep0[n] = 0; s_depn[n] = jb + 1; n++; }
+		}
+		s_ndeps = n;
 	}
 	__syncthreads();
 
@@ -460,16 +466,18 @@ stream_collide_persistent_kernel(const __grid_constant__ StepParams<T> p, const 
 	T *dst = p.dst;
 	for (int t = 0; t < q.nsteps; t++) {
 		if (t > 0) {
-			if (poll) {
+			if (threadIdx.x < 32) {                          // warp 0: one dependency per lane, polled concurrently
 				unsigned long long t0 = 0;
-				for (uint32_t c = ia; c <= ib; c++) {
-					while (ld_acquire_gpu(q.progress + c) < t) {
-						if (t0 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-						unsigned long long now;
-						asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-						if (now - t0 > q.timeout_ns || ld_acquire_gpu(q.abort)) { *q.abort = 1; s_abort = 1; break; }
-					}
-				}
+				uint32_t spins = 0;
+				for (int k = 0; k < s_ndeps; k++)
+					for (uint32_t c = s_dep0[k] + lane; c < s_dep0[k] + s_depn[k]; c += 32)
+						while (ld_acquire_gpu(q.progress + c) < t) {
+							if ((++spins & 255u) != 0) continue;         // look at the clock only now and then
+							unsigned long long now;
+							asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+							if (t0 == 0) t0 = now;
+							if (now - t0 > q.timeout_ns || ld_acquire_gpu(q.abort)) { *q.abort = 1; s_abort = 1; break; }
+						}
 			}
 			__syncthreads();
 			if (s_abort) return;

@@ -46,15 +46,19 @@ def _assert_same(got, want, what):
 # ---------------------------------------------------------------------------------------------
 # against the golden vectors of the compiled reference (every case, incl. 10,000 steps)
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("persistent", [-1, 0, 1], ids=["auto", "per-step-launch", "persistent"])
+ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), "graph": dict(graph=3),
+           "graph+pdl": dict(graph=4, pdl=1)}
+
+
+@pytest.mark.parametrize("engine", list(ENGINES))
 @pytest.mark.parametrize("name", list(cases.CASES))
-def test_cuda_matches_reference_golden(name, persistent):
+def test_cuda_matches_reference_golden(name, engine):
     c, g = cases.CASES[name], GOLDEN[name]
-    if persistent == 0 and c["steps"] > 1000:
-        pytest.skip("10,000-step cases run once per engine")
+    if engine in ("pdl", "graph") and c["steps"] > 1000:
+        pytest.skip("10,000-step cases: default, persistent and graph+pdl engines only")
     fA, walls = cases.make_inputs(name)
     with _lattice(c) as lat:
-        lat.set_tuning(persistent=persistent)
+        lat.set_tuning(**ENGINES[engine])
         lat.upload(fA, walls)
         lat.run(c["steps"])
         a, b = lat.download("A"), lat.download("B")
@@ -87,13 +91,13 @@ def test_cuda_matches_oracle_shapes(prec, isa, shape):
         walls[:] = 0                           # no channel rows when the lattice is 1-2 rows high
         walls[0, ::5] = 1
     o = _oracle(c, fA, walls, c["steps"])
-    for persistent in (0, 1):
+    for engine, tune in ENGINES.items():
         with _lattice(c) as lat:
-            lat.set_tuning(persistent=persistent)
+            lat.set_tuning(**tune)
             lat.upload(fA, walls)
             lat.run(c["steps"])
-            _assert_same(lat.download("A"), o.f_view("A"), f"fA persistent={persistent}")
-            _assert_same(lat.download("B"), o.f_view("B"), f"fB persistent={persistent}")
+            _assert_same(lat.download("A"), o.f_view("A"), f"fA engine={engine}")
+            _assert_same(lat.download("B"), o.f_view("B"), f"fB engine={engine}")
 
 
 def _variants(prec):
@@ -108,7 +112,10 @@ def _variants(prec):
             dict(vec=2, neighbour=0, hints=1, block=512, ctas_per_sm=1, persistent=0),
             dict(vec=2, neighbour=0, hints=0, block=64, ctas_per_sm=8, persistent=0),
             dict(vec=2, neighbour=0, hints=0, block=512, ctas_per_sm=1, persistent=1),
-            dict(vec=vecs[-1], neighbour=1, hints=0, block=64, ctas_per_sm=3, persistent=1)]
+            dict(vec=vecs[-1], neighbour=1, hints=0, block=64, ctas_per_sm=3, persistent=1),
+            dict(vec=1, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=1, graph=2),
+            dict(vec=vecs[-1], neighbour=0, hints=1, block=256, ctas_per_sm=4, persistent=0, pdl=1, graph=0),
+            dict(vec=2, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=0, graph=1)]
     return out
 
 
@@ -119,7 +126,7 @@ def test_every_kernel_variant_is_bit_identical(prec):
     o = _oracle(c, fA, walls, c["steps"])
     with _lattice(c) as lat:
         for tune in _variants(prec):
-            lat.set_tuning(**tune)
+            lat.set_tuning(**dict(dict(pdl=0, graph=0), **tune))
             lat.upload(fA, walls)
             lat.run(c["steps"])
             _assert_same(lat.download("A"), o.f_view("A"), f"fA with {tune}")

@@ -1,0 +1,66 @@
+"""Multi-GPU parity check, one rank per GPU (torchrun): the slab ring over N GPUs must reproduce the
+single-GPU lattice bit for bit, for both transports (peer-to-peer stores with device flags; staged NCCL).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/mgpu_check.py
+"""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from latticeboltzmann_b200 import Lattice  # noqa: E402
+from latticeboltzmann_b200.slab import DistributedLattice  # noqa: E402
+from tests import cases  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    ok = True
+    for prec, transport, nx, ny in (("dp", "p2p", 803, 2000), ("sp", "p2p", 803, 2000), ("dp", "staged", 401, 1000),
+                                    ("dp", "p2p", world, 64), ("sp", "p2p", 2 * world + 1, 264)):
+        c = dict(prec=prec, isa="avx", nx=nx, ny=ny, scene="cylinder" if nx > 100 else "random", perturb=None if nx > 100 else 3)
+        fA, walls = cases.make_inputs(c)
+        dl = DistributedLattice(nx, ny, prec, transport, device=local)
+        dl.lat.upload(fA, walls)
+        dist.barrier()
+        t0 = time.time()
+        dl.run(20)
+        dl.run(40)
+        mine = dl.lat.download_slab()
+        mine_b = dl.lat.download_slab(which="B")
+        dt = time.time() - t0
+        re = dl.gather_reynolds()
+        parts, parts_b = [None] * world, [None] * world
+        dist.all_gather_object(parts, mine)
+        dist.all_gather_object(parts_b, mine_b)
+        if rank == 0:
+            with Lattice(nx, ny, prec, device=local) as one:
+                one.upload(fA, walls)
+                one.run(60)
+                want, want_b, want_re = one.download("A"), one.download("B"), one.ComputeReynolds()
+            got, got_b = np.concatenate(parts, axis=1), np.concatenate(parts_b, axis=1)
+            same = got.tobytes() == want.tobytes() and got_b.tobytes() == want_b.tobytes() and re == want_re
+            ok &= same
+            print(f"[mgpu] {prec} {transport} {nx}x{ny} over {world} GPUs: {'BIT-EXACT' if same else 'MISMATCH'} vs single GPU "
+                  f"(Re {re!r} vs {want_re!r}; {dt:.2f} s)", flush=True)
+            if not same:
+                bad = np.argwhere(got != want)
+                print("   first differing elements (s,i,j):", bad[:5].tolist(), flush=True)
+        dl.close()
+        dist.barrier()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -29,18 +29,22 @@ def main():
             with Lattice(nx, ny, prec) as lat:
                 lat.InitializeArrays(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=nx // 10)
                 lat.run_timed(T)
-                combos = list(itertools.product(vecs, (0, 1), (0, 1), (128, 256), (0,), (0,)))
-                combos += list(itertools.product(vecs, (0, 1), (0,), (128, 256, 512), (0, 1, 2, 3, 4, 6, 8), (1,)))
-                for vec, nb, hints, block, ctas, pers in combos:
-                    if quick and (block != 256 or ctas not in (0,)):
+                MODES = {"stream": dict(persistent=0, pdl=0, graph=0), "pdl": dict(persistent=0, pdl=1, graph=0),
+                         "graph": dict(persistent=0, pdl=0, graph=10), "graph+pdl": dict(persistent=0, pdl=1, graph=10),
+                         "persistent": dict(persistent=1, pdl=0, graph=0)}
+                combos = list(itertools.product(vecs, (0, 1), (0, 1), (128, 256), (0,), ("stream",)))
+                combos += list(itertools.product(vecs, (0, 1), (0,), (64, 128, 256), (0,), ("pdl", "graph", "graph+pdl")))
+                combos += list(itertools.product(vecs, (0, 1), (0,), (128, 256, 512), (0, 2, 4), ("persistent",)))
+                for vec, nb, hints, block, ctas, mode in combos:
+                    if quick and block != 128:
                         continue
-                    if pers and vec == 1 and nb == 0:
-                        continue                     # vec 1 has no shuffle variant
-                    lat.set_tuning(vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas, persistent=pers)
+                    if vec == 1 and nb == 0:
+                        continue                     # vec 1 has no shuffle variant (identical code to nb 1)
+                    lat.set_tuning(vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas, **MODES[mode])
                     lat.run_timed(max(2, T // 10))
                     ms = min(lat.run_timed(T) for _ in range(2))
                     mlups = nx * ny * T / (ms * 1e-3) / 1e6
-                    rec = dict(prec=prec, nx=nx, ny=ny, T=T, vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas, persistent=pers,
+                    rec = dict(prec=prec, nx=nx, ny=ny, T=T, vec=vec, neighbour=nb, hints=hints, block=block, ctas_per_sm=ctas, mode=mode,
                                ms=round(ms, 3), mlups=round(mlups, 1), gbs=round(mlups * BYTES[prec] / 1e3, 1),
                                frac=round(mlups * BYTES[prec] / 1e3 / peak, 4))
                     out.append(rec)
@@ -49,11 +53,11 @@ def main():
     json.dump(out, open(os.path.join(ROOT, "gpurun_out", "sweep.json"), "w"), indent=0)
     for prec in ("dp", "sp"):
         for nx, ny, _ in lattices:
-            for pers in (0, 1):
-              best = sorted((r for r in out if r["prec"] == prec and r["nx"] == nx and r["persistent"] == pers), key=lambda r: -r["mlups"])[:4]
-              print(f"== best {prec} {nx}x{ny} persistent={pers}")
+            for mode in ("stream", "pdl", "graph", "graph+pdl", "persistent"):
+              best = sorted((r for r in out if r["prec"] == prec and r["nx"] == nx and r["mode"] == mode), key=lambda r: -r["mlups"])[:3]
+              print(f"== best {prec} {nx}x{ny} {mode}")
               for r in best:
-                print("  ", {k: r[k] for k in ("persistent", "vec", "neighbour", "hints", "block", "ctas_per_sm", "mlups", "gbs", "frac")})
+                print("  ", {k: r[k] for k in ("mode", "vec", "neighbour", "hints", "block", "ctas_per_sm", "mlups", "gbs", "frac")})
 
 
 if __name__ == "__main__":
