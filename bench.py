@@ -32,6 +32,7 @@ BYTES_PER_UPDATE = {"dp": 144, "sp": 72}      # 9 reads + 9 writes of real_t, SU
 DTYPE_NAME = {"dp": "f64", "sp": "f32"}
 C2 = dict(nx=400, ny=4000, timesteps=10000)   # BASELINE.json configs[1]
 WEAK = dict(nx_per_gpu=8192, ny=32768, timesteps=100)   # BASELINE.json configs[4]
+STRONG = dict(nx=16384, ny=65536, timesteps=100)        # BASELINE.json configs[3]
 
 
 def measured_peak():
@@ -291,7 +292,12 @@ def bench_multi(args):
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     peak, peak_src = measured_peak()
-    nx, ny, T = WEAK["nx_per_gpu"] * world, WEAK["ny"], WEAK["timesteps"]
+    strong = args.workload == "strong"
+    if strong:      # BASELINE configs[3]: 16384x65536 DP over 2/4/8 GPUs (77 GB per buffer: needs >= 2 GPUs)
+        nx, ny, T, precs = STRONG["nx"], STRONG["ny"], STRONG["timesteps"], ("dp",)
+    else:           # BASELINE configs[4]: 8192x32768 sites per GPU
+        nx, ny, T, precs = WEAK["nx_per_gpu"] * world, WEAK["ny"], WEAK["timesteps"], ("dp", "sp")
+    rows_per_gpu = nx // world
     out = {}
     sampler, clocks = ClockSampler(local), None
 
@@ -300,9 +306,9 @@ def bench_multi(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    for prec in ("dp", "sp"):
+    for prec in precs:
         dl = DistributedLattice(nx, ny, prec, transport=args.transport, device=local)
-        scene = dict(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=WEAK["nx_per_gpu"] // 10)
+        scene = dict(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=min(nx, ny) // 10)
         dl.lat.InitializeArrays(**scene)
         dl.lat.sync()
         for _ in range(args.warmup):
@@ -326,11 +332,11 @@ def bench_multi(args):
         mlups = nx * ny * T * args.steps / (total_ms * 1e-3) / 1e6
         res = {"value": round(mlups, 1), "ms_per_step": round(total_ms / args.steps, 3), "launches": launches,
                "wall_ms_per_step": round(1e3 * wall / args.steps, 3),
-               "roofline": roofline(prec, WEAK["nx_per_gpu"] * ny, T * args.steps, T * args.steps, total_ms, peak, peak_src)}
+               "roofline": roofline(prec, rows_per_gpu * ny, T * args.steps, T * args.steps, total_ms, peak, peak_src)}
         res["reynolds"] = dl.gather_reynolds()
 
         # e2e: every rank uploads its slab from host memory, runs, downloads it again
-        need = 9 * WEAK["nx_per_gpu"] * ny * (8 if prec == "dp" else 4) * 1.15
+        need = 9 * rows_per_gpu * ny * (8 if prec == "dp" else 4) * 1.15
         avail = 0
         try:
             avail = int(re.search(r"MemAvailable:\s+(\d+)", open("/proc/meminfo").read()).group(1)) * 1024
@@ -367,16 +373,18 @@ def bench_multi(args):
     if rank == 0:
         dp = out["dp"]
         line = {"metric": "MLUPS", "value": dp["value"], "unit": "MLUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": dp["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": dp["ms_per_step"], "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"BASELINE configs[4]: weak scaling, {WEAK['nx_per_gpu']}x{ny} sites per GPU, DP (SP under 'sp'), {world} B200",
+                "config": {"workload": (f"BASELINE configs[3]: strong scaling, {nx}x{ny} lattice DP, slab-partitioned over {world} B200" if strong else
+                                        f"BASELINE configs[4]: weak scaling, {WEAK['nx_per_gpu']}x{ny} sites per GPU, DP (SP under 'sp'), {world} B200"),
                            "lattice": f"{nx}x{ny}", "timesteps_per_step": T, "scene": "channel walls + disc obstacle, tau 0.7, accel 0.005",
                            "parallelism": f"row slabs x{world}, halo rows stored peer-to-peer over NVLink ({args.transport}), boundary rows on a second stream",
-                           "l2": "38.6 GB (DP) per GPU, far larger than L2"},
+                           "l2": "tens of GB per GPU, far larger than L2"},
                 "roofline": dp["roofline"], "e2e": dp["e2e"], "gpu_launches": dp["launches"], "clocks": clocks,
                 "reynolds": dp["reynolds"], "achieved_gbs_per_gpu": dp["roofline"]["achieved"],
-                "wall_ms_per_step": dp["wall_ms_per_step"],
-                "sp": {k: out["sp"][k] for k in ("value", "ms_per_step", "roofline", "e2e", "reynolds")}}
+                "wall_ms_per_step": dp["wall_ms_per_step"]}
+        if "sp" in out:
+            line["sp"] = {k: out["sp"][k] for k in ("value", "ms_per_step", "roofline", "e2e", "reynolds")}
         print(json.dumps(line), flush=True)
     dist.destroy_process_group()
     return 0
@@ -390,6 +398,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--transport", default="p2p", choices=["p2p", "staged"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="auto", choices=["auto", "weak", "strong"],
+                    help="N > 1 only: weak = 8192x32768 per GPU (default), strong = 16384x65536 over all ranks")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
