@@ -6,10 +6,11 @@
  * prec_float_cuda.h, otherwise prec_double_cuda.h, and link the matching library.
  *
  * The reference's compile-time #defines (LB.c:46-56) are command-line arguments here:
- *   lbm_b200_{dp,sp} [NX NY NTIMESTEPS [NGPU [SCENE [DUMP_EVERY]]]]
+ *   lbm_b200_{dp,sp} [NX NY NTIMESTEPS [NGPU [SCENE [DUMP_EVERY [INPLACE]]]]]
  *     SCENE: 0 = InitializeArrays (channel + barrier, LB.c:559-578)
  *            1 = channel + disc obstacle (BASELINE config 3: centre (NX/2, NY/5), radius NX/10)
  *     DUMP_EVERY > 0 writes data/<step>.csv like SAVELATTICE (LB.c:155-159; data/ must exist)
+ *     INPLACE = 1: one buffer per slab instead of fA/fB (lbm_config.inplace), same fA after every DoTimeStep
  * Defaults reproduce the shipped program: 400 x 2000, 10000 steps.
  */
 #ifdef LBM_DRIVER_FLOAT
@@ -91,19 +92,21 @@ static int reynolds(real_t *re)
 
 int main(int argc, char **argv)
 {
-	int scene_id = 0, dump_every = 0;
+	int scene_id = 0, dump_every = 0, inplace = 0;
 	if (argc >= 4) { NX = atoi(argv[1]); NY = atoi(argv[2]); NTIMESTEPS = atoi(argv[3]); }
 	if (argc >= 5) NGPU = atoi(argv[4]);
 	if (argc >= 6) scene_id = atoi(argv[5]);
 	if (argc >= 7) dump_every = atoi(argv[6]);
+	if (argc >= 8) inplace = atoi(argv[7]) != 0;
 	if (NGPU < 1 || NGPU > MAXGPU || NX < NGPU || (NTIMESTEPS & 1)) {
 		fprintf(stderr, "usage: %s [NX NY NTIMESTEPS(even) [NGPU [SCENE [DUMP_EVERY]]]]\n", argv[0]);
 		return EXIT_FAILURE;
 	}
 
 	/* LB.c:136-137 (the reference prints "%lf.2 MB") */
-	printf("Lattice Size: %dx%d (%.2lf MB per buffer, %s, %d GPU%s)\n", NX, NY,
-	       (double)NX * NY * NSPEEDS * sizeof(real_t) / 1024.0 / 1024.0, LBM_PREC_TAG, NGPU, NGPU > 1 ? "s" : "");
+	printf("Lattice Size: %dx%d (%.2lf MB per buffer, %s, %d GPU%s%s)\n", NX, NY,
+	       (double)NX * NY * NSPEEDS * sizeof(real_t) / 1024.0 / 1024.0, LBM_PREC_TAG, NGPU, NGPU > 1 ? "s" : "",
+	       inplace ? ", one buffer in place" : "");
 
 	lbm_scene scene = lbm_scene_reference();
 	if (scene_id == 1) {
@@ -114,6 +117,7 @@ int main(int argc, char **argv)
 		lbm_config cfg = {0};
 		cfg.nx = NX; cfg.ny = NY; cfg.tau = TAU; cfg.accel = ACCEL;
 		cfg.device = g;
+		cfg.inplace = inplace;
 		cfg.row_lo = (int)((long long)NX * g / NGPU);
 		cfg.row_hi = (int)((long long)NX * (g + 1) / NGPU);
 		CHECK(lbm_create(&slabs[g], &cfg));

@@ -58,6 +58,12 @@ typedef struct {
 	int device;        /* CUDA device ordinal */
 	int row_lo, row_hi;/* this slab owns global rows [row_lo,row_hi); 0,0 = whole lattice.
 	                      The reference's MPI row-slab decomposition (README.md:44-53). */
+	int inplace;       /* 0: A/B double buffer as LB.c:186-210 (fA and fB both observable).
+	                      1: ONE buffer, in-place "AA pattern" streaming: half the memory, the
+	                      working set of a step is the lattice once instead of twice.  Buffer A
+	                      after every DoTimeStep / even step count is bit-identical to the
+	                      A/B result; buffer B does not exist (fB arguments must be NULL,
+	                      lbm_stream_collide and the staged halo transport are refused). */
 } lbm_config;
 
 /* Closed-form scenes.  lbm_scene_reference() is InitializeArrays (LB.c:551-606). */

@@ -28,7 +28,7 @@ def _structs(real):
     class Config(ctypes.Structure):
         _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int), ("tau", real), ("accel", real),
                     ("vecwidth", ctypes.c_int), ("device", ctypes.c_int),
-                    ("row_lo", ctypes.c_int), ("row_hi", ctypes.c_int)]
+                    ("row_lo", ctypes.c_int), ("row_hi", ctypes.c_int), ("inplace", ctypes.c_int)]
 
     class Scene(ctypes.Structure):
         _fields_ = [("rho0", real), ("channel_walls", ctypes.c_int),

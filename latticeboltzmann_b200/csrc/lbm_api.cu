@@ -57,6 +57,7 @@ struct IpcBlob {           // what lbm_ipc_export ships (<= LBM_IPC_BLOB_BYTES)
 	cudaIpcMemHandle_t flags;
 	int nxl, ny, device, pid;
 	unsigned long long uid;
+	int inplace;
 };
 static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "blob too large");
 
@@ -65,8 +66,9 @@ static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "blob too large");
 struct lbm_ctx {
 	lbm_config cfg;
 	int nxl, ny, vw, nyvec, ldy, ldw;
+	int inplace;                 // one buffer, AA-pattern steps (lbm_config.inplace)
 	size_t plane;
-	real_t *f[2];
+	real_t *f[2];                // f[1] == nullptr when inplace
 	uint32_t *mask;
 	int *flags;                  // device int[4]: [0] from dn, [1] from up, [3] timeout
 	cudaStream_t stream[2];      // 0 main (inner rows), 1 boundary rows
@@ -112,7 +114,9 @@ int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_
 StepParams<real_t> make_params(const lbm_ctx *c, int src, int r0, int r1, int tail_source)
 {
 	StepParams<real_t> p;
-	const int dst = src ^ 1;
+	/* in place: `src` only selects the phase (0 -> phase 1, 1 -> phase 2); one buffer everywhere */
+	const int dst = c->inplace ? 0 : src ^ 1;
+	if (c->inplace) src = 0;
 	p.src = c->f[src];
 	p.dst = c->f[dst];
 	p.mask = c->mask;
@@ -159,6 +163,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (cfg->nx < 1 || cfg->ny < 2) return fail(LBM_ERR_ARG, "lbm_create: lattice %dx%d too small", cfg->nx, cfg->ny);
 	int vw = cfg->vecwidth ? cfg->vecwidth : VECWIDTH;
 	if (vw != 1 && vw != 2 && vw != 4 && vw != 8) return fail(LBM_ERR_ARG, "lbm_create: vecwidth %d not in {1,2,4,8}", vw);
+	if (cfg->inplace != 0 && cfg->inplace != 1) return fail(LBM_ERR_ARG, "lbm_create: inplace %d not in {0,1}", cfg->inplace);
 	int lo = cfg->row_lo, hi = cfg->row_hi;
 	if (lo == 0 && hi == 0) hi = cfg->nx;
 	if (lo < 0 || hi > cfg->nx || lo >= hi) return fail(LBM_ERR_ARG, "lbm_create: bad slab rows [%d,%d) of %d", lo, hi, cfg->nx);
@@ -198,13 +203,14 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	c->a58 = cfg->accel * c->w58;
 
 	const size_t fbytes = 9 * c->plane * sizeof(real_t);
+	c->inplace = cfg->inplace ? 1 : 0;
 	cudaError_t e = cudaMalloc(&c->f[0], fbytes);
-	if (e == cudaSuccess) e = cudaMalloc(&c->f[1], fbytes);
+	if (e == cudaSuccess && !c->inplace) e = cudaMalloc(&c->f[1], fbytes);
 	if (e == cudaSuccess) e = cudaMalloc(&c->mask, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMalloc(&c->flags, 4 * sizeof(int));
 	if (e == cudaSuccess) e = cudaMalloc(&c->progress, (PROGRESS_SLOTS + 1) * sizeof(int));
 	if (e == cudaSuccess) e = cudaMemset(c->f[0], 0, fbytes);
-	if (e == cudaSuccess) e = cudaMemset(c->f[1], 0, fbytes);
+	if (e == cudaSuccess && c->f[1]) e = cudaMemset(c->f[1], 0, fbytes);
 	if (e == cudaSuccess) e = cudaMemset(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMemset(c->flags, 0, 4 * sizeof(int));
 	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaStreamCreateWithFlags(&c->stream[k], cudaStreamNonBlocking);
@@ -213,7 +219,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (e == cudaSuccess) e = cudaEventCreate(&c->ev_t0);
 	if (e == cudaSuccess) e = cudaEventCreate(&c->ev_t1);
 	if (e != cudaSuccess) {
-		fail(LBM_ERR_CUDA, "lbm_create: %s (%.2f GB requested)", cudaGetErrorString(e), 2.0 * fbytes / 1e9);
+		fail(LBM_ERR_CUDA, "lbm_create: %s (%.2f GB requested)", cudaGetErrorString(e), (c->inplace ? 1.0 : 2.0) * fbytes / 1e9);
 		lbm_destroy(c);
 		return LBM_ERR_CUDA;
 	}
@@ -268,20 +274,31 @@ int lbm_destroy(lbm_ctx *c)
 // ---------------------------------------------------------------------------
 namespace {
 
-template <int V, int NB, int HINT>
-cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
+typedef void (*step_kernel_t)(const StepParams<real_t>);
+
+cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
 {
-	if (!pdl) {
-		stream_collide_vec_kernel<real_t, V, NB, HINT><<<grid, block, 0, st>>>(p);
-		return cudaGetLastError();
-	}
 	cudaLaunchConfig_t cfg = {};
 	cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
 	cudaLaunchAttribute at[1];
 	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 	at[0].val.programmaticStreamSerializationAllowed = 1;
-	cfg.attrs = at; cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, stream_collide_vec_kernel<real_t, V, NB, HINT>, p);
+	cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+	return cudaLaunchKernelEx(&cfg, kern, p);
+}
+
+template <int V, int NB, int HINT>
+cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
+{
+	return launch_kernel(stream_collide_vec_kernel<real_t, V, NB, HINT>, p, grid, block, st, pdl);
+}
+
+/* in-place (AA) step kernels: phase 1 (from the reference layout) / phase 2 (back to it) */
+template <int V>
+cudaError_t launch_aa_v(int phase, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
+{
+	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1>, p, grid, block, st, pdl)
+	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2>, p, grid, block, st, pdl);
 }
 
 template <int V>
@@ -324,6 +341,18 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		/* PDL only where consecutive step kernels follow each other on one stream with nothing between */
 		const int pdl = c->tune.pdl && c->sync_mode == SYNC_SELF && c->nyvec == c->ny;
 		cudaError_t e;
+		if (c->inplace) {
+			const int phase = src == 0 ? 1 : 2;
+			switch (V) {
+			case 1: e = launch_aa_v<1>(phase, p, (unsigned)grid, block, st, pdl); break;
+			case 2: e = launch_aa_v<2>(phase, p, (unsigned)grid, block, st, pdl); break;
+			case 4: e = launch_aa_v<4>(phase, p, (unsigned)grid, block, st, pdl); break;
+#ifdef LBM_FLOAT
+			case 8: e = launch_aa_v<8>(phase, p, (unsigned)grid, block, st, pdl); break;
+#endif
+			default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
+			}
+		} else
 		switch (V) {
 		case 1: e = launch_vec_v<1>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
 		case 2: e = launch_vec_v<2>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
@@ -344,7 +373,9 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		unsigned long long grid = (total + block - 1) / block;
 		const unsigned long long cap = (unsigned long long)sm_count(c->cfg.device) * 16;
 		if (grid > cap) grid = cap;
-		stream_collide_scalar_kernel<real_t><<<(unsigned)grid, block, 0, st>>>(p);
+		if (!c->inplace) stream_collide_scalar_kernel<real_t, 0><<<(unsigned)grid, block, 0, st>>>(p);
+		else if (src == 0) stream_collide_scalar_kernel<real_t, 1><<<(unsigned)grid, block, 0, st>>>(p);
+		else stream_collide_scalar_kernel<real_t, 2><<<(unsigned)grid, block, 0, st>>>(p);
 		cudaError_t e = cudaGetLastError();
 		if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_scalar_kernel: %s", cudaGetErrorString(e));
 		c->launches++;
@@ -401,7 +432,7 @@ int launch_persistent(lbm_ctx *c, int src, int nsteps, int last_tail, cudaStream
 
 bool use_persistent(const lbm_ctx *c)
 {
-	if (c->sync_mode != SYNC_SELF || c->vw <= 1 || c->nyvec != c->ny) return false;
+	if (c->sync_mode != SYNC_SELF || c->vw <= 1 || c->nyvec != c->ny || c->inplace) return false;
 	return c->tune.persistent != 0;
 }
 
@@ -502,7 +533,7 @@ int lbm_initialize_arrays(lbm_ctx *c, const lbm_scene *scene)
 	CK(cudaGetLastError());
 	/* INITIALDENSITY * OMEGA_s in real_t (LB.c:583-591) */
 	scene_fill_kernel<real_t><<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(
-		c->f[0], c->f[1], c->plane, c->ldy, c->nxl, c->ny, scene->rho0 * c->w0, scene->rho0 * c->w14, scene->rho0 * c->w58);
+		c->f[0], c->f[1] /* nullptr when in place */, c->plane, c->ldy, c->nxl, c->ny, scene->rho0 * c->w0, scene->rho0 * c->w14, scene->rho0 * c->w58);
 	CK(cudaGetLastError());
 	c->launches += 2;
 	c->has_state = 1;
@@ -514,6 +545,7 @@ static int upload_impl(lbm_ctx *c, const real_t *fA, const real_t *fB, const cha
 {
 	if (!c || !fA || !walls) return fail(LBM_ERR_ARG, "lbm_upload: null argument");
 	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_upload: ldy %d < ny %d", ldy, c->ny);
+	if (fB && c->inplace) return fail(LBM_ERR_STATE, "lbm_upload: an in-place context has no buffer B (pass fB = NULL)");
 	int rc;
 	if ((rc = set_device(c))) return rc;
 	cudaStream_t st = c->stream[0];
@@ -522,7 +554,7 @@ static int upload_impl(lbm_ctx *c, const real_t *fA, const real_t *fB, const cha
 	for (int b = 0; b < 2; b++) {
 		const real_t *src = b == 0 ? fA : fB;
 		if (!src) {                                              /* fB = 0 (LB.c:593-601) */
-			CK(cudaMemsetAsync(c->f[1], 0, 9 * c->plane * sizeof(real_t), st));
+			if (c->f[1]) CK(cudaMemsetAsync(c->f[1], 0, 9 * c->plane * sizeof(real_t), st));
 			continue;
 		}
 		for (int s = 0; s < 9; s++)
@@ -568,6 +600,7 @@ static int download_impl(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, in
 {
 	if (!c) return fail(LBM_ERR_ARG, "lbm_download: null ctx");
 	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_download: ldy %d < ny %d", ldy, c->ny);
+	if (fB && c->inplace) return fail(LBM_ERR_STATE, "lbm_download: an in-place context has no buffer B");
 	int rc;
 	if ((rc = lbm_sync(c))) return rc;
 	cudaStream_t st = c->stream[0];
@@ -694,6 +727,7 @@ int lbm_apply_source(lbm_ctx *c, int buf)
 {
 	if (!c || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_apply_source: bad argument");
 	if (c->sync_mode != SYNC_SELF) return fail(LBM_ERR_STATE, "lbm_apply_source: single-slab contexts only (use lbm_run)");
+	if (c->inplace && buf != 0) return fail(LBM_ERR_STATE, "lbm_apply_source: an in-place context has no buffer B");
 	int rc;
 	if ((rc = set_device(c))) return rc;
 	if ((rc = launch_source(c, buf, c->stream[0]))) return rc;
@@ -705,6 +739,8 @@ int lbm_stream_collide(lbm_ctx *c, int src_buf)
 	if (!c || (src_buf != 0 && src_buf != 1)) return fail(LBM_ERR_ARG, "lbm_stream_collide: bad argument");
 	if (c->sync_mode != SYNC_SELF) return fail(LBM_ERR_STATE, "lbm_stream_collide: single-slab contexts only (use lbm_run)");
 	if (!c->has_state) return fail(LBM_ERR_STATE, "lbm_stream_collide: no lattice loaded");
+	if (c->inplace) return fail(LBM_ERR_STATE, "lbm_stream_collide: in-place contexts step in pairs (lbm_do_timestep / lbm_run); "
+	                                            "between the two steps of a pair the buffer is not in the reference layout");
 	int rc;
 	if ((rc = set_device(c))) return rc;
 	/* the source buffer may have been written by upload/apply_source: make its halo rows current */
@@ -871,7 +907,8 @@ int lbm_ipc_export(lbm_ctx *c, unsigned char blob[LBM_IPC_BLOB_BYTES])
 	memset(&b, 0, sizeof b);
 	memcpy(b.magic, "LBMIPC1", 8);
 	CK(cudaIpcGetMemHandle(&b.f[0], c->f[0]));
-	CK(cudaIpcGetMemHandle(&b.f[1], c->f[1]));
+	if (!c->inplace) CK(cudaIpcGetMemHandle(&b.f[1], c->f[1]));
+	b.inplace = c->inplace;
 	CK(cudaIpcGetMemHandle(&b.flags, c->flags));
 	b.nxl = c->nxl; b.ny = c->ny; b.device = c->cfg.device;
 	b.uid = (unsigned long long)(uintptr_t)c->f[0] ^ ((unsigned long long)c->cfg.row_lo << 48);
@@ -892,10 +929,12 @@ int lbm_ipc_connect(lbm_ctx *c, const unsigned char up[LBM_IPC_BLOB_BYTES], cons
 	for (int k = 0; k < 2; k++) {
 		if (memcmp(b[k].magic, "LBMIPC1", 8)) return fail(LBM_ERR_ARG, "lbm_ipc_connect: bad blob");
 		if (b[k].ny != c->ny) return fail(LBM_ERR_ARG, "lbm_ipc_connect: neighbour ny %d != %d", b[k].ny, c->ny);
+		if (b[k].inplace != c->inplace) return fail(LBM_ERR_ARG, "lbm_ipc_connect: neighbour and this slab differ in lbm_config.inplace");
 		if (k == 1 && !memcmp(&b[0], &b[1], sizeof(IpcBlob))) { peer[1] = peer[0]; break; }   /* P == 2: one neighbour, both sides */
-		void *ptr[3];
+		void *ptr[3] = {nullptr, nullptr, nullptr};
 		const cudaIpcMemHandle_t *h[3] = {&b[k].f[0], &b[k].f[1], &b[k].flags};
 		for (int m = 0; m < 3; m++) {
+			if (m == 1 && c->inplace) continue;
 			CK(cudaIpcOpenMemHandle(&ptr[m], *h[m], cudaIpcMemLazyEnablePeerAccess));
 			c->ipc_opened[c->n_ipc_opened++] = ptr[m];
 		}
@@ -915,6 +954,7 @@ int lbm_connect_local(lbm_ctx *c, lbm_ctx *up, lbm_ctx *dn)
 {
 	if (!c || !up || !dn) return fail(LBM_ERR_ARG, "lbm_connect_local: null argument");
 	if (up->ny != c->ny || dn->ny != c->ny) return fail(LBM_ERR_ARG, "lbm_connect_local: ny mismatch");
+	if (up->inplace != c->inplace || dn->inplace != c->inplace) return fail(LBM_ERR_ARG, "lbm_connect_local: slabs differ in lbm_config.inplace");
 	lbm_ctx *nb[2] = {up, dn};
 	for (int k = 0; k < 2; k++) {
 		if (nb[k]->cfg.device != c->cfg.device) {
@@ -984,6 +1024,7 @@ int lbm_group_run(lbm_ctx **slabs, int n, int nsteps)
 int lbm_halo_pack(lbm_ctx *c, int buf, void *to_up, void *to_dn)
 {
 	if (!c || !to_up || !to_dn || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_halo_pack: bad argument");
+	if (c->inplace) return fail(LBM_ERR_STATE, "lbm_halo_pack: the staged transport needs the A/B layout (in-place slabs exchange by peer stores)");
 	int rc;
 	if ((rc = set_device(c))) return rc;
 	halo_pack_kernel<real_t><<<(c->ny + 255) / 256, 256, 0, c->stream[1]>>>(c->f[buf], (real_t *)to_up, (real_t *)to_dn, c->plane, c->ldy, c->nxl, c->ny);
@@ -995,6 +1036,7 @@ int lbm_halo_pack(lbm_ctx *c, int buf, void *to_up, void *to_dn)
 int lbm_halo_unpack(lbm_ctx *c, int buf, const void *from_dn, const void *from_up)
 {
 	if (!c || !from_dn || !from_up || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_halo_unpack: bad argument");
+	if (c->inplace) return fail(LBM_ERR_STATE, "lbm_halo_unpack: the staged transport needs the A/B layout (in-place slabs exchange by peer stores)");
 	int rc;
 	if ((rc = set_device(c))) return rc;
 	halo_unpack_kernel<real_t><<<(c->ny + 255) / 256, 256, 0, c->stream[1]>>>(c->f[buf], (const real_t *)from_dn, (const real_t *)from_up, c->plane, c->ldy, c->nxl, c->ny);

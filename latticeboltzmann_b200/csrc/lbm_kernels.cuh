@@ -268,6 +268,36 @@ template <typename T> __device__ __forceinline__ void source_site(T (&o)[9], con
 }
 
 // ---------------------------------------------------------------------------
+// wall bits + collide/bounce + tail source for the V sites (r, j0..j0+V-1) whose pulled
+// populations are f[s][k]; returns the wall bits of the V sites (LB.c:437-475)
+// ---------------------------------------------------------------------------
+template <typename T, int V>
+__device__ __forceinline__ uint32_t relax_sites(const StepParams<T> &p, const T (&f)[9][V], T (&o)[9][V], int r, int j0, int tail_source)
+{
+	// wall bits of my V sites and of my aligned VECWIDTH group (LB.c:437-440)
+	const uint32_t word = __ldg(p.mask + (size_t)r * p.ldw + (j0 >> 5));
+	const uint32_t sh = (uint32_t)j0 & 31u;
+	const uint32_t bits = (word >> sh) & ((1u << V) - 1u);
+	bool dbl = false;
+	if (sizeof(T) == 4) dbl = ((word >> (sh & ~(uint32_t)(p.vw - 1))) & ((1u << p.vw) - 1u)) != 0u;
+#pragma unroll
+	for (int k = 0; k < V; k++) {
+		T fk[9], ok[9];
+#pragma unroll
+		for (int s = 0; s < 9; s++) fk[s] = f[s][k];
+		if ((bits >> k) & 1u) {
+			bounce<T>(fk, ok);
+		} else {
+			collide_vec_order<T>(fk, ok, p, dbl);
+			if (k == 0 && j0 == 0 && tail_source) source_site<T>(ok, p);
+		}
+#pragma unroll
+		for (int s = 0; s < 9; s++) o[s][k] = ok[s];
+	}
+	return bits;
+}
+
+// ---------------------------------------------------------------------------
 // the fused pull update of one V-wide vector of sites (StreamCollideVec, LB.c:307-484,
 // + tail ApplySource + halo push)
 //   V     sites per thread (contiguous in j, V*sizeof(T) <= 32 bytes)
@@ -333,28 +363,8 @@ __device__ __forceinline__ void update_vector(const StepParams<T> &p, const T *_
 		}
 	}
 
-	// wall bits of my V sites and of my aligned VECWIDTH group (LB.c:437-440)
-	const uint32_t word = __ldg(p.mask + (size_t)r * p.ldw + (j0 >> 5));
-	const uint32_t sh = (uint32_t)j0 & 31u;
-	const uint32_t bits = (word >> sh) & ((1u << V) - 1u);
-	bool dbl = false;
-	if (sizeof(T) == 4) dbl = ((word >> (sh & ~(uint32_t)(p.vw - 1))) & ((1u << p.vw) - 1u)) != 0u;
-
 	T o[9][V];
-#pragma unroll
-	for (int k = 0; k < V; k++) {
-		T fk[9], ok[9];
-#pragma unroll
-		for (int s = 0; s < 9; s++) fk[s] = f[s][k];
-		if ((bits >> k) & 1u) {
-			bounce<T>(fk, ok);
-		} else {
-			collide_vec_order<T>(fk, ok, p, dbl);
-			if (k == 0 && j0 == 0 && tail_source) source_site<T>(ok, p);
-		}
-#pragma unroll
-		for (int s = 0; s < 9; s++) o[s][k] = ok[s];
-	}
+	const uint32_t bits = relax_sites<T, V>(p, f, o, r, j0, tail_source);
 
 	if (active) {
 		T *d = dst + (size_t)(r + 1) * p.ldy + j0;
@@ -398,6 +408,162 @@ stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 		const bool active = g0 < total;
 		const uint32_t g = active ? g0 : total - 1;          // idle lanes shadow the last vector (loads stay legal)
 		update_vector<T, V, NB, HINT, false>(p, p.src, p.dst, nvec, g, active, lane, p.tail_source);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// In-place streaming ("AA pattern": ONE buffer instead of the A/B pair of LB.c:186-210).
+// Every site reads nine slots and stores its nine results into the SAME nine slots, so no
+// other site's data is ever overwritten and no second buffer is needed.  Steps alternate:
+//   PHASE 1 (steps 1,3,5,... of a run; memory holds the reference layout, slot s of site x =
+//            post-collide f_s of x): site x pulls f_s from slot s of (x - e_s) exactly like the
+//            A/B kernel (LB.c:235-243) and stores its post-collide o_s into the slot it read
+//            f_opp(s) from, i.e. slot opp(s) of site (x + e_s).
+//   PHASE 2 (steps 2,4,6,...): site x finds what the pull of the next step would fetch, f_s, in
+//            slot opp(s) of x itself; it stores o_s into slot s of x -- the reference layout again,
+//            so after every DoTimeStep (two steps, LB.c:186-210) buffer A is bit-identical to
+//            the reference's fA.  Purely local: no neighbour rows, perfectly aligned accesses.
+// Wall sites write back exactly what they read (bounce-back, LB.c:246-255, maps slot to itself),
+// which also keeps the stale f0 of wall sites.  The arithmetic is relax_sites(), shared with the
+// A/B kernel.  Loads are coherent (never ld.global.nc): the buffer is written by this kernel.
+//
+// Slab seams: phase 1 reads rows i-1 / i+1 of boundary rows from the halo rows (filled by the
+// neighbours' phase-2 push) and stores straight into the NEIGHBOUR'S OWNED boundary row (peer
+// memory, or this slab itself when P == 1); phase 2 pushes the three halo speeds like the A/B
+// kernel does.  Same bytes over NVLink per two steps as A/B.
+// ---------------------------------------------------------------------------
+template <int V> __device__ __forceinline__ void ldc(const double *p, double (&v)[V])
+{
+	if constexpr (V == 1) v[0] = *p;
+	else {
+#pragma unroll
+		for (int k = 0; k < V; k += 2) { const double2 t = *reinterpret_cast<const double2 *>(p + k); v[k] = t.x; v[k + 1] = t.y; }
+	}
+}
+template <int V> __device__ __forceinline__ void ldc(const float *p, float (&v)[V])
+{
+	if constexpr (V == 1) v[0] = *p;
+	else if constexpr (V == 2) { const float2 t = *reinterpret_cast<const float2 *>(p); v[0] = t.x; v[1] = t.y; }
+	else {
+#pragma unroll
+		for (int k = 0; k < V; k += 4) { const float4 t = *reinterpret_cast<const float4 *>(p + k); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
+	}
+}
+// V values to columns (j0-1 .. j0+V-2) [DJ < 0, first one wraps to jl] or (j0+1 .. j0+V) [DJ > 0, last one wraps to jr]
+template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(T *row, int j0, int jl, int jr, const T (&v)[V])
+{
+	if constexpr (DJ < 0) {
+		row[jl] = v[0];
+		if constexpr (V == 2) row[j0] = v[1];
+		if constexpr (V >= 4) {
+#pragma unroll
+			for (int k = 1; k + 1 < V; k += 2) {            // pairs (1,2),(3,4),... start at the even column j0+k-1
+				T pr[2] = {v[k], v[k + 1]};
+				stv<0, 2>(row + j0 + k - 1, pr);
+			}
+			row[j0 + V - 2] = v[V - 1];
+		}
+	} else {
+		row[jr] = v[V - 1];
+		if constexpr (V == 2) row[j0 + 1] = v[0];
+		if constexpr (V >= 4) {
+			row[j0 + 1] = v[0];
+#pragma unroll
+			for (int k = 1; k + 1 < V; k += 2) {            // pairs (1,2),(3,4),... land on the even column j0+k+1
+				T pr[2] = {v[k], v[k + 1]};
+				stv<0, 2>(row + j0 + k + 1, pr);
+			}
+		}
+	}
+}
+
+template <typename T, int V, int PHASE>
+__device__ __forceinline__ void update_vector_aa(const StepParams<T> &p, uint32_t nvec, uint32_t g, bool active, int tail_source)
+{
+	const uint32_t rr = g / nvec;
+	const uint32_t jv = g - rr * nvec;
+	const int r = p.r0 + (int)rr;
+	const int j0 = p.jmin + (int)jv * V;
+	T *const own = p.dst + (size_t)(r + 1) * p.ldy;          // p.src == p.dst
+	T f[9][V], o[9][V];
+
+	if constexpr (PHASE == 2) {
+#pragma unroll
+		for (int s = 0; s < 9; s++) ldc<V>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
+		relax_sites<T, V>(p, f, o, r, j0, tail_source);
+		if (active) {
+#pragma unroll
+			for (int s = 0; s < 9; s++) stv<0, V>(own + (size_t)s * p.plane + j0, o[s]);
+			if (r == 0) {                                    // as in the A/B kernel (LB.c:239,242,243)
+				stv<0, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
+				stv<0, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
+				stv<0, V>(p.dn_halo + 8 * p.dn_plane + j0, o[8]);
+			}
+			if (r == p.nxl - 1) {                            // (LB.c:237,240,241)
+				stv<0, V>(p.up_halo + 2 * p.up_plane + j0, o[2]);
+				stv<0, V>(p.up_halo + 5 * p.up_plane + j0, o[5]);
+				stv<0, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
+			}
+		}
+	} else {
+		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;          // LB.c:337-338
+		const int jr = j0 + V == p.ny ? 0 : j0 + V;
+		const T *lrow[3] = {own - p.ldy, own, own + p.ldy};  // rows i-1 (halo when r == 0), i, i+1 (halo when r == nxl-1)
+#pragma unroll
+		for (int s = 0; s < 9; s++) {
+			const T *b = lrow[pull_di(s) + 1] + (size_t)s * p.plane;
+			if constexpr (V == 1) {
+				f[s][0] = b[pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0];
+			} else {
+				T al[V];
+				ldc<V>(b + j0, al);
+				if (pull_dj(s) == 0) {
+#pragma unroll
+					for (int k = 0; k < V; k++) f[s][k] = al[k];
+				} else if (pull_dj(s) < 0) {
+					f[s][0] = b[jl];
+#pragma unroll
+					for (int k = 1; k < V; k++) f[s][k] = al[k - 1];
+				} else {
+					f[s][V - 1] = b[jr];
+#pragma unroll
+					for (int k = 0; k < V - 1; k++) f[s][k] = al[k + 1];
+				}
+			}
+		}
+		relax_sites<T, V>(p, f, o, r, j0, tail_source);
+		if (active) {
+			// slot k of site (x - e_k) receives o[opp(k)]; rows beyond the slab are the neighbour's owned boundary rows
+			T *srow[3];
+			size_t spl[3];
+			srow[1] = own;              spl[1] = p.plane;
+			if (r == 0) { srow[0] = p.dn_halo - p.ldy; spl[0] = p.dn_plane; } else { srow[0] = own - p.ldy; spl[0] = p.plane; }
+			if (r == p.nxl - 1) { srow[2] = p.up_halo + p.ldy; spl[2] = p.up_plane; } else { srow[2] = own + p.ldy; spl[2] = p.plane; }
+#pragma unroll
+			for (int k = 0; k < 9; k++) {
+				T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
+				if (pull_dj(k) == 0) stv<0, V>(b + j0, o[opposite(k)]);
+				else if (pull_dj(k) < 0) st_shifted<T, V, -1>(b, j0, jl, jr, o[opposite(k)]);
+				else st_shifted<T, V, 1>(b, j0, jl, jr, o[opposite(k)]);
+			}
+		}
+	}
+}
+
+template <typename T, int V, int PHASE>
+__global__ void __launch_bounds__(512)
+stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
+{
+	asm volatile("griddepcontrol.launch_dependents;");
+	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
+	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {
+		const uint32_t g0 = base + threadIdx.x;
+		const bool active = g0 < total;
+		const uint32_t g = active ? g0 : total - 1;
+		update_vector_aa<T, V, PHASE>(p, nvec, g, active, p.tail_source);
 	}
 }
 
@@ -503,7 +669,8 @@ stream_collide_persistent_kernel(const __grid_constant__ StepParams<T> p, const 
 // the ragged tail j >= NYVECMAX of a vector build, or everything when the
 // matched reference build is a prec_*_serial.h one.  One site per thread.
 // ---------------------------------------------------------------------------
-template <typename T>
+// PHASE 0: A/B (src -> dst); 1, 2: the in-place phases described at update_vector_aa.
+template <typename T, int PHASE>
 __global__ void __launch_bounds__(256)
 stream_collide_scalar_kernel(const __grid_constant__ StepParams<T> p)
 {
@@ -515,18 +682,44 @@ stream_collide_scalar_kernel(const __grid_constant__ StepParams<T> p)
 		const int j = p.jmin + (int)(g - rr * ncol);
 		const int jl = j == 0 ? p.ny - 1 : j - 1;
 		const int jr = j + 1 == p.ny ? 0 : j + 1;
-		const T *row0 = p.src + (size_t)r * p.ldy;
 		T f[9], o[9];
+		if (PHASE == 0) {
+			const T *row0 = p.src + (size_t)r * p.ldy;
 #pragma unroll
-		for (int s = 0; s < 9; s++) {
-			const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j;
-			f[s] = __ldg(row0 + (size_t)(pull_di(s) + 1) * p.ldy + (size_t)s * p.plane + jj);
+			for (int s = 0; s < 9; s++) {
+				const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j;
+				f[s] = __ldg(row0 + (size_t)(pull_di(s) + 1) * p.ldy + (size_t)s * p.plane + jj);
+			}
+		} else if (PHASE == 1) {
+			const T *row0 = p.dst + (size_t)r * p.ldy;
+#pragma unroll
+			for (int s = 0; s < 9; s++) {
+				const int jj = pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j;
+				f[s] = row0[(size_t)(pull_di(s) + 1) * p.ldy + (size_t)s * p.plane + jj];
+			}
+		} else {
+			const T *site = p.dst + (size_t)(r + 1) * p.ldy + j;
+#pragma unroll
+			for (int s = 0; s < 9; s++) f[s] = site[(size_t)opposite(s) * p.plane];
 		}
 		const bool wall = (__ldg(p.mask + (size_t)r * p.ldw + (j >> 5)) >> (j & 31)) & 1u;
 		if (wall) bounce<T>(f, o);
 		else {
 			collide_scalar_order<T>(f, o, p);
 			if (j == 0 && p.tail_source) source_site<T>(o, p);
+		}
+		if (PHASE == 1) {
+			T *own = p.dst + (size_t)(r + 1) * p.ldy;
+#pragma unroll
+			for (int k = 0; k < 9; k++) {
+				const int jj = pull_dj(k) < 0 ? jl : pull_dj(k) > 0 ? jr : j;
+				T *b;
+				if (pull_di(k) < 0) b = r == 0 ? p.dn_halo - p.ldy + (size_t)k * p.dn_plane : own - p.ldy + (size_t)k * p.plane;
+				else if (pull_di(k) > 0) b = r == p.nxl - 1 ? p.up_halo + p.ldy + (size_t)k * p.up_plane : own + p.ldy + (size_t)k * p.plane;
+				else b = own + (size_t)k * p.plane;
+				b[jj] = o[opposite(k)];
+			}
+			continue;
 		}
 		T *d = p.dst + (size_t)(r + 1) * p.ldy + j;
 		if (!wall) d[0] = o[0];
@@ -639,7 +832,7 @@ __global__ void scene_fill_kernel(T *fA, T *fB, size_t plane, int ldy, int nxl, 
 #pragma unroll
 	for (int s = 0; s < 9; s++) {
 		fA[o + s * plane] = s == 0 ? v0 : (s <= 4 ? v14 : v58);
-		fB[o + s * plane] = T(0);
+		if (fB) fB[o + s * plane] = T(0);
 	}
 }
 

@@ -90,6 +90,8 @@ class DistributedLattice:
         self.rank = dist.get_rank(group) if rank is None else rank
         self.world = dist.get_world_size(group) if world is None else world
         self.group, self.transport = group, transport
+        if kw.get("inplace") and transport == "staged" and self.world > 1:
+            raise ValueError("the staged transport needs the A/B layout; in-place slabs exchange by peer stores (transport='p2p')")
         self.bounds = partition_rows(nx, self.world)
         lo, hi = self.bounds[self.rank]
         if device is None:

@@ -17,11 +17,14 @@ def _ptr(a):
 
 
 class Lattice:
-    def __init__(self, nx, ny, prec="dp", tau=0.7, accel=0.005, vecwidth=0, device=0, row_lo=0, row_hi=0):
+    def __init__(self, nx, ny, prec="dp", tau=0.7, accel=0.005, vecwidth=0, device=0, row_lo=0, row_hi=0, inplace=False):
+        """``inplace=True`` keeps ONE buffer and steps with the in-place (AA) kernels: buffer A after every
+        even step count is bit-identical, buffer B does not exist (lbm_config.inplace)."""
         self.lib = _capi.load(prec)
+        self.inplace = bool(inplace)
         self.prec, self.dtype = prec, self.lib.dtype
         self.nx, self.ny = int(nx), int(ny)
-        cfg = self.lib.Config(self.nx, self.ny, tau, accel, vecwidth, device, row_lo, row_hi)
+        cfg = self.lib.Config(self.nx, self.ny, tau, accel, vecwidth, device, row_lo, row_hi, int(self.inplace))
         self._ctx = ctypes.c_void_p()
         self.lib.check(self.lib.dll.lbm_create(ctypes.byref(self._ctx), ctypes.byref(cfg)))
         self.tau = cfg.tau

@@ -47,7 +47,16 @@ def _assert_same(got, want, what):
 # against the golden vectors of the compiled reference (every case, incl. 10,000 steps)
 # ---------------------------------------------------------------------------------------------
 ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), "graph": dict(graph=3),
-           "graph+pdl": dict(graph=4, pdl=1)}
+           "graph+pdl": dict(graph=4, pdl=1),
+           # one buffer, in-place (AA) kernels (lbm_config.inplace): only buffer A exists
+           "inplace": dict(inplace=1), "inplace+graph+pdl": dict(inplace=1, graph=4, pdl=1)}
+
+
+def _split(engine_kw):
+    """(constructor kwargs, tuning kwargs) of an ENGINES entry"""
+    kw = dict(engine_kw)
+    ctor = {"inplace": True} if kw.pop("inplace", 0) else {}
+    return ctor, kw
 
 
 @pytest.mark.parametrize("engine", list(ENGINES))
@@ -57,19 +66,23 @@ def test_cuda_matches_reference_golden(name, engine):
     if engine in ("pdl", "graph") and c["steps"] > 1000:
         pytest.skip("10,000-step cases: default, persistent and graph+pdl engines only")
     fA, walls = cases.make_inputs(name)
-    with _lattice(c) as lat:
-        lat.set_tuning(**ENGINES[engine])
+    ctor, tune = _split(ENGINES[engine])
+    with _lattice(c, **ctor) as lat:
+        lat.set_tuning(**tune)
         lat.upload(fA, walls)
         lat.run(c["steps"])
-        a, b = lat.download("A"), lat.download("B")
+        a = lat.download("A")
+        b = None if ctor else lat.download("B")
         assert cases.digest(a) == g["fA_sha256"], f"fA differs from the reference after {c['steps']} steps"
-        assert cases.digest(b) == g["fB_sha256"], "fB differs (odd step with its source applied, LB.c:201)"
+        if b is not None:
+            assert cases.digest(b) == g["fB_sha256"], "fB differs (odd step with its source applied, LB.c:201)"
         assert float(lat.ComputeReynolds()).hex() == g["reynolds_hex"]
         _assert_same(lat.download_walls(), walls, "wall mask round trip")
         if c.get("full"):
             z = np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz"))
             _assert_same(a, z["fA"], "fA")
-            _assert_same(b, z["fB"], "fB")
+            if b is not None:
+                _assert_same(b, z["fB"], "fB")
 
 
 # ---------------------------------------------------------------------------------------------
@@ -91,13 +104,15 @@ def test_cuda_matches_oracle_shapes(prec, isa, shape):
         walls[:] = 0                           # no channel rows when the lattice is 1-2 rows high
         walls[0, ::5] = 1
     o = _oracle(c, fA, walls, c["steps"])
-    for engine, tune in ENGINES.items():
-        with _lattice(c) as lat:
+    for engine, ekw in ENGINES.items():
+        ctor, tune = _split(ekw)
+        with _lattice(c, **ctor) as lat:
             lat.set_tuning(**tune)
             lat.upload(fA, walls)
             lat.run(c["steps"])
             _assert_same(lat.download("A"), o.f_view("A"), f"fA engine={engine}")
-            _assert_same(lat.download("B"), o.f_view("B"), f"fB engine={engine}")
+            if not ctor:
+                _assert_same(lat.download("B"), o.f_view("B"), f"fB engine={engine}")
 
 
 def _variants(prec):
@@ -131,6 +146,17 @@ def test_every_kernel_variant_is_bit_identical(prec):
             lat.run(c["steps"])
             _assert_same(lat.download("A"), o.f_view("A"), f"fA with {tune}")
             _assert_same(lat.download("B"), o.f_view("B"), f"fB with {tune}")
+    # the in-place kernels: every vector width, a few CTA shapes, capped grids, PDL/graph
+    vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
+    with _lattice(c, inplace=True) as lat:
+        for v in vecs:
+            for extra in (dict(block=128), dict(block=256, ctas_per_sm=2), dict(block=64, pdl=1, graph=2), dict(block=512, ctas_per_sm=1, pdl=1)):
+                tune = dict(dict(vec=v, neighbour=1, hints=0, ctas_per_sm=0, persistent=0, pdl=0, graph=0), **extra)
+                lat.set_tuning(**tune)
+                lat.upload(fA, walls)
+                lat.run(4)
+                lat.run(c["steps"] - 4)
+                _assert_same(lat.download("A"), o.f_view("A"), f"in-place fA with {tune}")
 
 
 @pytest.mark.parametrize("prec", ["dp", "sp"])
@@ -191,13 +217,26 @@ def test_error_behaviour():
         lat.run(0)
     with pytest.raises(LbmError):
         Lattice(0, 16)
+    # an in-place context has one buffer: everything that names buffer B or a single step is refused
+    with Lattice(8, 16, inplace=True) as lat:
+        f, w = np.zeros((9, 8, 16)) + 0.1, np.zeros((8, 16), dtype=np.int8)
+        with pytest.raises(LbmError):
+            lat.upload(f, w, fB=f)
+        lat.upload(f, w)
+        lat.run(2)
+        for bad in (lambda: lat.download("B"), lambda: lat.StreamCollide("A"), lambda: lat.ApplySource("B"), lambda: lat.run(1)):
+            with pytest.raises(LbmError):
+                bad()
+        lat.ApplySource("A")
+        assert lat.slab_info().dev_f[1] is None
 
 
 # ---------------------------------------------------------------------------------------------
 # decomposition invariance: N logical slabs on one GPU == one slab, bit for bit
 # ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("inplace", [False, True], ids=["ab", "inplace"])
 @pytest.mark.parametrize("prec,nslabs", [("dp", 2), ("dp", 3), ("dp", 8), ("sp", 4)])
-def test_slab_ring_equals_single_slab(prec, nslabs):
+def test_slab_ring_equals_single_slab(prec, nslabs, inplace):
     from latticeboltzmann_b200 import Lattice, group_run, make_ring
     c = dict(prec=prec, isa="avx", nx=200, ny=1000, scene="cylinder", perturb=None, steps=60)
     fA, walls = cases.make_inputs(c)
@@ -205,7 +244,7 @@ def test_slab_ring_equals_single_slab(prec, nslabs):
         one.upload(fA, walls)
         one.run(c["steps"])
         want_a, want_b, want_re = one.download("A"), one.download("B"), one.ComputeReynolds()
-    ring = make_ring(c["nx"], c["ny"], nslabs, prec)
+    ring = make_ring(c["nx"], c["ny"], nslabs, prec, inplace=inplace)
     try:
         for s in ring:
             s.upload(fA, walls)
@@ -214,9 +253,11 @@ def test_slab_ring_equals_single_slab(prec, nslabs):
         got_a, got_b = np.zeros_like(want_a), np.zeros_like(want_b)
         for s in ring:
             s.download("A", out=got_a)
-            s.download("B", out=got_b)
+            if not inplace:
+                s.download("B", out=got_b)
         _assert_same(got_a, want_a, "fA over the ring")
-        _assert_same(got_b, want_b, "fB over the ring")
+        if not inplace:
+            _assert_same(got_b, want_b, "fB over the ring")
         cols = [s.reynolds_column() for s in ring]
         re = ring[0].reynolds_from_column(np.concatenate([u for u, _ in cols]), np.concatenate([f for _, f in cols]))
         assert re == want_re
@@ -230,8 +271,9 @@ def test_uneven_slabs_and_single_row_slabs():
     c = dict(prec="dp", isa="avx", nx=11, ny=64, scene="random", perturb=9, steps=10)
     fA, walls = cases.make_inputs(c)
     o = _oracle(c, fA, walls, c["steps"])
-    for bounds in ([(0, 1), (1, 2), (2, 11)], [(0, 5), (5, 6), (6, 11)], [(k, k + 1) for k in range(11)]):
-        ring = make_ring(c["nx"], c["ny"], len(bounds), "dp", bounds=bounds)
+    for bounds, inplace in [(b, ip) for b in ([(0, 1), (1, 2), (2, 11)], [(0, 5), (5, 6), (6, 11)], [(k, k + 1) for k in range(11)])
+                            for ip in (False, True)]:
+        ring = make_ring(c["nx"], c["ny"], len(bounds), "dp", bounds=bounds, inplace=inplace)
         try:
             for s in ring:
                 s.upload(fA, walls)
@@ -239,7 +281,7 @@ def test_uneven_slabs_and_single_row_slabs():
             got = np.zeros_like(fA)
             for s in ring:
                 s.download("A", out=got)
-            _assert_same(got, o.f_view("A"), f"ring {bounds}")
+            _assert_same(got, o.f_view("A"), f"ring {bounds} inplace={inplace}")
         finally:
             for s in ring:
                 s.close()
@@ -248,14 +290,15 @@ def test_uneven_slabs_and_single_row_slabs():
 # ---------------------------------------------------------------------------------------------
 # full BASELINE sizes: properties that need no CPU run
 # ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("inplace", [False, True], ids=["ab", "inplace"])
 @pytest.mark.parametrize("prec", ["dp", "sp"])
-def test_full_size_properties_400x4000(prec):
+def test_full_size_properties_400x4000(prec, inplace):
     """BASELINE config 2 at its full 10,000 steps: mass is conserved to rounding (source and
     bounce-back are conservative), wall-site f0 keeps its initial value (LB.c:246-255), the flow is
     finite and positive, and two chunked runs equal one long run bit for bit."""
     from latticeboltzmann_b200 import Lattice
     nx, ny, steps = 400, 4000, 10000
-    with Lattice(nx, ny, prec) as a, Lattice(nx, ny, prec) as b:
+    with Lattice(nx, ny, prec, inplace=inplace) as a, Lattice(nx, ny, prec) as b:
         a.InitializeArrays()
         b.InitializeArrays()
         f0 = a.download("A")
@@ -275,9 +318,10 @@ def test_full_size_properties_400x4000(prec):
 def test_c_driver_prints_reference_reynolds():
     """driver/main.c (the reference's main over the C ABI) on the shipped scenario: the final line's
     Re must be the compiled reference's value to all printed digits (LB.c:173, %.10le)."""
-    for tag, case in (("dp", "builtin_dp_10000"), ("sp", "builtin_sp_10000")):
+    for tag, case, extra in (("dp", "builtin_dp_10000", []), ("sp", "builtin_sp_10000", []),
+                             ("dp", "builtin_dp_10000", ["1", "0", "0", "1"]), ("sp", "builtin_sp_10000", ["1", "0", "0", "1"])):
         exe = os.path.join(ROOT, "driver", f"lbm_b200_{tag}")
-        out = subprocess.run([exe, "400", "2000", "10000"], capture_output=True, text=True, timeout=300)
+        out = subprocess.run([exe, "400", "2000", "10000"] + extra, capture_output=True, text=True, timeout=300)
         assert out.returncode == 0, out.stderr
         last = out.stdout.strip().splitlines()[-1]
         want = "%.10le" % float.fromhex(GOLDEN[case]["reynolds_hex"])
