@@ -179,6 +179,13 @@ typedef struct {
 	int pdl;          /* 1: step kernels are launched with programmatic dependent launch, so the next
 	                     step's CTAs are resident (waiting in griddepcontrol.wait) while this one drains */
 	int graph;        /* >0: steps are replayed from a captured CUDA graph of `graph` step pairs */
+	int tb_depth;     /* in-place single-slab contexts only.  >= 2 (even): temporal blocking in L2 -- the lattice
+	                     is swept in bands of tb_rows rows, and each band is advanced tb_depth timesteps (one
+	                     kernel launch per band and timestep, band shifted down one row per timestep) while it
+	                     is L2-resident, so HBM sees each site once per tb_depth steps instead of every step.
+	                     Possible because the in-place kernels have no write-after-read hazards: a row may take
+	                     step t as soon as rows i-1, i, i+1 have taken step t-1.  0 = off (one launch per step). */
+	int tb_rows;      /* band height H in rows; 0 = chosen so that (H + tb_depth) rows take ~40 MB */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);

@@ -44,7 +44,7 @@ def _structs(real):
     class Tuning(ctypes.Structure):
         _fields_ = [("vec", ctypes.c_int), ("block", ctypes.c_int), ("neighbour", ctypes.c_int),
                     ("hints", ctypes.c_int), ("ctas_per_sm", ctypes.c_int), ("persistent", ctypes.c_int),
-                    ("pdl", ctypes.c_int), ("graph", ctypes.c_int)]
+                    ("pdl", ctypes.c_int), ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int)]
 
     return Config, Scene, SlabInfo, Tuning
 

@@ -87,6 +87,9 @@ struct lbm_ctx {
 	int *progress;               // persistent kernel: per-CTA step counters [PROGRESS_SLOTS] + abort word
 	cudaGraphExec_t graph_exec;  // captured `graph_pairs` x (A->B, B->A) steps with the current tuning
 	int graph_pairs;
+	cudaGraphExec_t wf_exec;     // captured wavefront macro-step (wf_k timesteps, bands of wf_h rows)
+	int wf_k, wf_h;
+	long long wf_launches;       // kernels in that graph
 };
 
 namespace {
@@ -107,6 +110,9 @@ void drop_graph(lbm_ctx *c)
 	if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
 	c->graph_exec = nullptr;
 	c->graph_pairs = 0;
+	if (c->wf_exec) cudaGraphExecDestroy(c->wf_exec);
+	c->wf_exec = nullptr;
+	c->wf_k = c->wf_h = 0;
 }
 
 int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_OK; }
@@ -241,6 +247,17 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	 * 43.7 vs 41.1 GLUPS at 400x4000 (profiles/r01_run3); no gain for SP or for large lattices */
 	c->tune.pdl = default_small_dp(c);
 	c->tune.graph = default_small_dp(c) ? 10 : 0;
+	if (c->inplace && (unsigned long long)c->nxl * c->ny <= (16ull << 20)) {
+		/* in-place small lattices (profiles/r01_run8, r01_run9): PDL + graph replay for both precisions; lattices
+		 * beyond what the L2 keeps (~60 MB) whose rows are narrow enough for >= 64-row bands are swept with
+		 * temporal blocking (DP 400x4000: 59.3 vs 43.8 GLUPS, DP 800x4000 57.0 vs 44.7, SP 800x4000 90.0 vs 83.5) */
+		c->tune.pdl = 1;
+		c->tune.graph = 10;
+		const double row_bytes = 9.0 * c->ldy * sizeof(real_t);
+		const int k = sizeof(real_t) == 8 ? 16 : 8;
+		const double band = sizeof(real_t) == 8 ? 45e6 : 60e6;
+		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) c->tune.tb_depth = k;
+	}
 	*out = c;
 	return LBM_OK;
 }
@@ -276,10 +293,10 @@ namespace {
 
 typedef void (*step_kernel_t)(const StepParams<real_t>);
 
-cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
 {
 	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+	cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
 	cudaLaunchAttribute at[1];
 	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 	at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -290,12 +307,12 @@ cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, unsig
 template <int V, int NB, int HINT>
 cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
 {
-	return launch_kernel(stream_collide_vec_kernel<real_t, V, NB, HINT>, p, grid, block, st, pdl);
+	return launch_kernel(stream_collide_vec_kernel<real_t, V, NB, HINT>, p, dim3(grid), block, st, pdl);
 }
 
 /* in-place (AA) step kernels: phase 1 (from the reference layout) / phase 2 (back to it) */
 template <int V>
-cudaError_t launch_aa_v(int phase, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_aa_v(int phase, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
 {
 	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1>, p, grid, block, st, pdl)
 	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2>, p, grid, block, st, pdl);
@@ -343,12 +360,21 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		cudaError_t e;
 		if (c->inplace) {
 			const int phase = src == 0 ? 1 : 2;
+			/* x: the vectors of one row; y: rows, capped (grid-stride) by ctas_per_sm and by the 65535 limit */
+			const unsigned gx = ((unsigned)(c->nyvec / V) + block - 1) / block;
+			unsigned gy = rows;
+			if (c->tune.ctas_per_sm > 0) {
+				const unsigned cap = (unsigned)(sm_count(c->cfg.device) * c->tune.ctas_per_sm) / gx;
+				if (gy > cap) gy = cap < 1 ? 1 : cap;
+			}
+			if (gy > 65535u) gy = 65535u;
+			const dim3 g2(gx, gy);
 			switch (V) {
-			case 1: e = launch_aa_v<1>(phase, p, (unsigned)grid, block, st, pdl); break;
-			case 2: e = launch_aa_v<2>(phase, p, (unsigned)grid, block, st, pdl); break;
-			case 4: e = launch_aa_v<4>(phase, p, (unsigned)grid, block, st, pdl); break;
+			case 1: e = launch_aa_v<1>(phase, p, g2, block, st, pdl); break;
+			case 2: e = launch_aa_v<2>(phase, p, g2, block, st, pdl); break;
+			case 4: e = launch_aa_v<4>(phase, p, g2, block, st, pdl); break;
 #ifdef LBM_FLOAT
-			case 8: e = launch_aa_v<8>(phase, p, (unsigned)grid, block, st, pdl); break;
+			case 8: e = launch_aa_v<8>(phase, p, g2, block, st, pdl); break;
 #endif
 			default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 			}
@@ -496,6 +522,89 @@ int enqueue_step(lbm_ctx *c, int src, int tail_source)
 		return LBM_OK;
 	}
 	return fail(LBM_ERR_STATE, "slab is wired with lbm_connect_local: step it through lbm_group_run");
+}
+
+// ---------------------------------------------------------------------------
+// Temporal blocking in L2 (in-place, single slab).  The in-place kernels only have read-after-write
+// dependencies: row i may take timestep t as soon as rows i-1, i, i+1 (periodic) have taken t-1.
+// One "macro-step" advances the whole ring k timesteps (levels s = 0..k-1) as
+//   pyramid          rows [s, H0-s)                       H0 >= 2k
+//   parallelograms   rows [a-s, b-s) for bands [a,b) of H rows tiling [H0, nx)     band after band
+//   inverted pyramid rows [nx-s, nx+s) mod nx             closes the periodic ring
+// Each (band, level) is one launch of the ordinary in-place kernel on a row range; stream order
+// satisfies every dependency.  A band of H+k rows stays L2-resident while it takes its k steps, so
+// HBM traffic per site update drops from 18 reals to ~18/k.  Results are bit-identical: the same
+// kernels do the same arithmetic on the same values, only the order of independent work changes.
+// ---------------------------------------------------------------------------
+int enqueue_macro(lbm_ctx *c, int t0, int k, int H0, int H, int nsteps)
+{
+	int rc;
+	const int nx = c->nxl;
+	for (int s = 0; s < k; s++)
+		if ((rc = launch_step(c, (t0 + s) & 1, s, H0 - s, t0 + s != nsteps - 1, c->stream[0]))) return rc;
+	for (int a = H0; a < nx; a += H) {
+		const int b = a + H < nx ? a + H : nx;
+		for (int s = 0; s < k; s++)
+			if ((rc = launch_step(c, (t0 + s) & 1, a - s, b - s, t0 + s != nsteps - 1, c->stream[0]))) return rc;
+	}
+	for (int s = 1; s < k; s++)
+		if ((rc = launch_step(c, (t0 + s) & 1, nx - s, nx + s, t0 + s != nsteps - 1, c->stream[0]))) return rc;
+	return LBM_OK;
+}
+
+int run_wavefront(lbm_ctx *c, int nsteps)
+{
+	int rc;
+	int k = c->tune.tb_depth & ~1;
+	const int nx = c->nxl;
+	while (k >= 2 && 2 * k + 2 > nx) k -= 2;                     /* pyramid base H0 >= 2k inside the ring */
+	if (k < 2) {
+		for (int t = 0; t < nsteps; t++)
+			if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
+		return LBM_OK;
+	}
+	int H = c->tune.tb_rows;
+	if (H <= 0) {                                                /* (H + k) rows ~ 45 MB (DP) / 60 MB (SP): measured best, profiles/r01_run9 */
+		const double row_bytes = 9.0 * c->ldy * sizeof(real_t);
+		H = (int)((sizeof(real_t) == 8 ? 45e6 : 60e6) / row_bytes) - k;
+	}
+	if (H < 2) H = 2;
+	int H0 = H < 2 * k ? 2 * k : H;
+	if (H0 > nx - 1) H0 = nx - 1;
+	if (nx - H0 > 0) {                                           /* equal bands over [H0, nx) instead of a short last one */
+		const int nb = (nx - H0 + H - 1) / H;
+		H = (nx - H0 + nb - 1) / nb;
+		if (H < 2) H = 2;
+	}
+	int t = 0;
+	if (c->tune.graph > 0 && nsteps - k >= k) {
+		if (!c->wf_exec || c->wf_k != k || c->wf_h != H) {
+			drop_graph(c);
+			cudaGraph_t g = nullptr;
+			CK(cudaStreamBeginCapture(c->stream[0], cudaStreamCaptureModeThreadLocal));
+			const long long l0 = c->launches;
+			rc = enqueue_macro(c, 0, k, H0, H, 1 << 30);         /* every level with its tail source */
+			c->wf_launches = c->launches - l0;
+			c->launches = l0;
+			cudaError_t e = cudaStreamEndCapture(c->stream[0], &g);
+			if (rc != LBM_OK) { if (g) cudaGraphDestroy(g); return rc; }
+			CK(e);
+			e = cudaGraphInstantiate(&c->wf_exec, g, 0);
+			cudaGraphDestroy(g);
+			CK(e);
+			c->wf_k = k; c->wf_h = H;
+		}
+		for (; nsteps - k - t >= k; t += k) {                    /* keep the last macro-step out: its last level leaves A un-sourced */
+			CK(cudaGraphLaunch(c->wf_exec, c->stream[0]));
+			c->launches += c->wf_launches;
+		}
+	}
+	while (t < nsteps) {
+		const int kk = nsteps - t < k ? nsteps - t : k;          /* even; H0 >= 2k >= 2kk */
+		if ((rc = enqueue_macro(c, t, kk, H0, H, nsteps))) return rc;
+		t += kk;
+	}
+	return LBM_OK;
 }
 
 // ApplySource + halo refresh + neighbour barrier that open every run (the first step's source
@@ -674,6 +783,7 @@ int lbm_run(lbm_ctx *c, int nsteps)
 	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
 	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
 	if (use_persistent(c)) return launch_persistent(c, LBM_BUF_A, nsteps, 0, c->stream[0]);
+	if (c->inplace && c->sync_mode == SYNC_SELF && c->tune.tb_depth >= 2) return run_wavefront(c, nsteps);
 	int t = 0;
 	if (c->tune.graph > 0 && c->sync_mode == SYNC_SELF) {
 		/* replay whole (A->B, B->A) pairs, all with the tail source, from a captured graph; the last
@@ -867,6 +977,10 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.persistent < 0 || n.persistent > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: persistent %d", n.persistent);
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
+	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
+	if (n.tb_rows < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d", n.tb_rows);
+	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
+	                                                           "the A/B buffers have write-after-read hazards between bands");
 	drop_graph(c);
 	c->tune = n;
 	return LBM_OK;

@@ -210,12 +210,16 @@ __device__ __forceinline__ void collide_vec_order(const T (&f)[9], T (&o)[9], co
 #pragma unroll
 	for (int s = 0; s < 9; s++) q[s] = A::mul(q[s], s == 0 ? r0 : (s <= 4 ? r14 : r58));
 	// Mixed group (LB.c:455-465): fluid lanes relax with 1/tau in double; only SP can tell the
-	// difference.  (Measured alternative: a warp-uniform branch around the fp64 code costs 14 more
-	// registers than letting ptxas predicate these few instructions off -- kept predicated.)
+	// difference.  ONE branch around all nine fp64 relaxations: groups with a wall are rare, and
+	// nine predicated-off cvt/dmul/dadd/cvt sequences per site cost issue slots the L2-resident
+	// (in-place, temporally blocked) runs are bound by.
+	if (sizeof(T) == 4 && dbl) {
 #pragma unroll
-	for (int s = 0; s < 9; s++) {
-		if (sizeof(T) == 4 && dbl) o[s] = relax_double<T>(f[s], q[s], p.itau_d);              // LB.c:456-464
-		else o[s] = A::add(f[s], A::mul(p.itau, A::sub(q[s], f[s])));                         // LB.c:442-450
+		for (int s = 0; s < 9; s++) o[s] = relax_double<T>(f[s], q[s], p.itau_d);             // LB.c:456-464
+	} else {
+		const T itau = p.itau;
+#pragma unroll
+		for (int s = 0; s < 9; s++) o[s] = A::add(f[s], A::mul(itau, A::sub(q[s], f[s])));    // LB.c:442-450
 	}
 }
 
@@ -478,11 +482,10 @@ template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(
 }
 
 template <typename T, int V, int PHASE>
-__device__ __forceinline__ void update_vector_aa(const StepParams<T> &p, uint32_t nvec, uint32_t g, bool active, int tail_source)
+__device__ __forceinline__ void update_vector_aa(const StepParams<T> &p, uint32_t rr, uint32_t jv, bool active, int tail_source)
 {
-	const uint32_t rr = g / nvec;
-	const uint32_t jv = g - rr * nvec;
-	const int r = p.r0 + (int)rr;
+	int r = p.r0 + (int)rr;
+	if (r >= p.nxl) r -= p.nxl;                              // row ranges of the wavefront schedule may wrap (r1 > nxl)
 	const int j0 = p.jmin + (int)jv * V;
 	T *const own = p.dst + (size_t)(r + 1) * p.ldy;          // p.src == p.dst
 	T f[9][V], o[9][V];
@@ -554,17 +557,15 @@ template <typename T, int V, int PHASE>
 __global__ void __launch_bounds__(512)
 stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 {
+	// 2-D grid: x over the vectors of a row, y over rows (grid-stride) -- no integer division per site
 	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
-	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
-	const uint32_t stride = gridDim.x * blockDim.x;
+	const uint32_t rows = (uint32_t)(p.r1 - p.r0);
+	const uint32_t jv = blockIdx.x * blockDim.x + threadIdx.x;
 	asm volatile("griddepcontrol.wait;" ::: "memory");
-	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {
-		const uint32_t g0 = base + threadIdx.x;
-		const bool active = g0 < total;
-		const uint32_t g = active ? g0 : total - 1;
-		update_vector_aa<T, V, PHASE>(p, nvec, g, active, p.tail_source);
-	}
+	if (jv >= nvec) return;
+	for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y)
+		update_vector_aa<T, V, PHASE>(p, rr, jv, true, p.tail_source);
 }
 
 // ---------------------------------------------------------------------------
@@ -678,7 +679,8 @@ stream_collide_scalar_kernel(const __grid_constant__ StepParams<T> p)
 	const uint32_t total = (uint32_t)(p.r1 - p.r0) * ncol;
 	for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
 		const uint32_t rr = g / ncol;
-		const int r = p.r0 + (int)rr;
+		int r = p.r0 + (int)rr;
+		if (PHASE != 0 && r >= p.nxl) r -= p.nxl;            // in-place wavefront schedule: wrapping row range
 		const int j = p.jmin + (int)(g - rr * ncol);
 		const int jl = j == 0 ? p.ny - 1 : j - 1;
 		const int jr = j + 1 == p.ny ? 0 : j + 1;

@@ -49,7 +49,10 @@ def _assert_same(got, want, what):
 ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), "graph": dict(graph=3),
            "graph+pdl": dict(graph=4, pdl=1),
            # one buffer, in-place (AA) kernels (lbm_config.inplace): only buffer A exists
-           "inplace": dict(inplace=1), "inplace+graph+pdl": dict(inplace=1, graph=4, pdl=1)}
+           "inplace": dict(inplace=1), "inplace+graph+pdl": dict(inplace=1, graph=4, pdl=1),
+           # + temporal blocking in L2: bands of tb_rows rows advanced tb_depth steps each (wavefront schedule)
+           "inplace+tb": dict(inplace=1, tb_depth=4, tb_rows=3),
+           "inplace+tb+graph+pdl": dict(inplace=1, tb_depth=6, tb_rows=5, graph=1, pdl=1)}
 
 
 def _split(engine_kw):
@@ -157,6 +160,17 @@ def test_every_kernel_variant_is_bit_identical(prec):
                 lat.run(4)
                 lat.run(c["steps"] - 4)
                 _assert_same(lat.download("A"), o.f_view("A"), f"in-place fA with {tune}")
+        # wavefront schedules: depth k, band height H (0 = automatic), with and without graph replay
+        for k, h, g in ((2, 0, 0), (4, 7, 0), (8, 16, 1), (46, 3, 0), (10, 200, 1), (4, 1, 1), (6, 90, 0)):
+            tune = dict(vec=vecs[-1], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=g, graph=g, tb_depth=k, tb_rows=h)
+            lat.set_tuning(**tune)
+            lat.upload(fA, walls)
+            lat.run(c["steps"])
+            _assert_same(lat.download("A"), o.f_view("A"), f"wavefront fA with {tune}")
+            lat.upload(fA, walls)
+            lat.run(2)
+            lat.run(c["steps"] - 2)
+            _assert_same(lat.download("A"), o.f_view("A"), f"wavefront fA (2 + {c['steps'] - 2} steps) with {tune}")
 
 
 @pytest.mark.parametrize("prec", ["dp", "sp"])

@@ -1,5 +1,6 @@
 """Short, deterministic workload for ncu: a few steps of the step kernel on the BASELINE lattices.
-usage: profile_target.py [dp|sp] [small|large] [nsteps]"""
+usage: profile_target.py [dp|sp] [small|large|c3] [nsteps] [ab|inplace]
+(inplace = one buffer, AA kernels, library-default temporal blocking -- what bench.py's headline runs)"""
 import os
 import sys
 
@@ -10,8 +11,13 @@ from latticeboltzmann_b200 import Lattice  # noqa: E402
 prec = sys.argv[1] if len(sys.argv) > 1 else "dp"
 size = sys.argv[2] if len(sys.argv) > 2 else "small"
 nsteps = int(sys.argv[3]) if len(sys.argv) > 3 else 20
-nx, ny = (400, 4000) if size == "small" else (8192, 32768)
-with Lattice(nx, ny, prec) as lat:
+engine = sys.argv[4] if len(sys.argv) > 4 else "ab"
+nx, ny = {"small": (400, 4000), "large": (8192, 32768), "c3": (800, 4000)}[size]
+with Lattice(nx, ny, prec, inplace=(engine == "inplace")) as lat:
     lat.InitializeArrays()
+    if engine == "inplace":
+        lat.set_tuning(graph=0)          # individual launches, so that ncu sees every kernel
+    l0 = lat.launches
     ms = lat.run_timed(nsteps)
-    print(f"{prec} {nx}x{ny}: {nsteps} steps in {ms:.3f} ms -> {nx * ny * nsteps / ms / 1e3:.1f} MLUPS, tuning {lat.get_tuning()}")
+    print(f"{prec} {nx}x{ny} {engine}: {nsteps} steps in {ms:.3f} ms -> {nx * ny * nsteps / ms / 1e3:.1f} MLUPS, "
+          f"{lat.launches - l0} launches, tuning {lat.get_tuning()}")
