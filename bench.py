@@ -238,18 +238,24 @@ def bench_single(args):
                 fA, walls = geometry.reference_scene(nx, ny, prec)
                 f_host[...] = fA
                 w_host[...] = walls
-                e2e_t = []
+                e2e_t, parts = [], [0.0, 0.0, 0.0]
                 for k in range(1 + args.steps):
                     lat.sync()
                     t0 = time.perf_counter()
                     lat.upload(f_host, w_host)
+                    t1 = time.perf_counter()
                     lat.run(T)
+                    t2 = time.perf_counter()
                     lat.download("A", out=o_host)
+                    t3 = time.perf_counter()
                     if k:
-                        e2e_t.append(time.perf_counter() - t0)
+                        e2e_t.append(t3 - t0)
+                        parts = [parts[0] + t1 - t0, parts[1] + t2 - t1, parts[2] + t3 - t2]
                 res["e2e"] = {"value": round(nx * ny * T * len(e2e_t) / sum(e2e_t) / 1e6, 1), "unit": "MLUPS",
                               "h2d_bytes_per_step": int(f_host.nbytes + w_host.nbytes), "d2h_bytes_per_step": int(o_host.nbytes),
-                              "ms_per_step": round(1e3 * sum(e2e_t) / len(e2e_t), 3)}
+                              "ms_per_step": round(1e3 * sum(e2e_t) / len(e2e_t), 3),
+                              "host_ms": {"upload": round(1e3 * parts[0] / len(e2e_t), 2), "enqueue": round(1e3 * parts[1] / len(e2e_t), 2),
+                                          "wait_and_download": round(1e3 * parts[2] / len(e2e_t), 2)}}
                 # parity stamp: the downloaded lattice must be the compiled reference's, bit for bit
                 try:
                     with open(os.path.join(ROOT, "tests", "golden", "golden.json")) as fh:
@@ -300,6 +306,39 @@ def bench_single(args):
     return 0
 
 
+def bench_strong_single(args):
+    """BASELINE configs[3] on ONE GPU: 16384x65536 DP is 77.3 GB per buffer, so only the in-place engine
+    (one buffer) fits the 180 GB of a B200 -- the N = 1 point of the strong-scaling series."""
+    import torch
+    from latticeboltzmann_b200 import Lattice
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device")
+    nx, ny, T = STRONG["nx"], STRONG["ny"], STRONG["timesteps"]
+    peak, peak_src = measured_peak()
+    with Lattice(nx, ny, "dp", inplace=True) as lat:
+        lat.InitializeArrays(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=min(nx, ny) // 10)
+        sampler = ClockSampler(0)
+        ms, launches = timed_jobs(lat, T, args.warmup, args.steps, lambda: None)
+        sampler.start()
+        ms, launches = timed_jobs(lat, T, 0, args.steps, lambda: None)
+        clocks = sampler.stop()
+        total_ms = sum(ms)
+        mlups = nx * ny * T * args.steps / (total_ms * 1e-3) / 1e6
+        line = {"metric": "MLUPS", "value": round(mlups, 1), "unit": "MLUPS", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": round(total_ms / args.steps, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"BASELINE configs[3]: strong scaling, {nx}x{ny} lattice DP on 1 B200", "lattice": f"{nx}x{ny}",
+                           "timesteps_per_step": T, "scene": "channel walls + disc obstacle, tau 0.7, accel 0.005",
+                           "engine": "in-place single buffer (77.3 GB; A+B would need 154.6 GB)", "l2": "77 GB lattice, far larger than L2"},
+                "roofline": roofline("dp", nx * ny, T * args.steps, step_kernel_launches(launches, args.steps, T), total_ms, peak, peak_src,
+                                     kernel="lbm::stream_collide_aa_kernel", traffic_key="dp_inplace_large"),
+                "e2e": {"value": None, "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                        "note": "skipped: a 77 GB host copy of the lattice is not part of this workload's N > 1 lines either (--no-e2e)"},
+                "gpu_launches": launches, "clocks": clocks, "reynolds": lat.ComputeReynolds(), "tuning": lat.get_tuning()}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
 def bench_multi(args):
     """torchrun, one rank per GPU: weak scaling, 8192x32768 sites per GPU, DP headline (+SP)."""
     import numpy as np
@@ -309,7 +348,10 @@ def bench_multi(args):
 
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
-    os.environ.setdefault("NCCL_DEBUG", "WARN")      # keep NCCL's version banner off stdout: one JSON line only
+    # NCCL prints its version banner on fd 1 whatever NCCL_DEBUG says: point fd 1 at stderr until the JSON line
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     peak, peak_src = measured_peak()
@@ -328,7 +370,7 @@ def bench_multi(args):
         return float(t.item())
 
     for prec in precs:
-        dl = DistributedLattice(nx, ny, prec, transport=args.transport, device=local)
+        dl = DistributedLattice(nx, ny, prec, transport=args.transport, device=local, inplace=(args.engine == "inplace"))
         scene = dict(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=min(nx, ny) // 10)
         dl.lat.InitializeArrays(**scene)
         dl.lat.sync()
@@ -353,7 +395,10 @@ def bench_multi(args):
         mlups = nx * ny * T * args.steps / (total_ms * 1e-3) / 1e6
         res = {"value": round(mlups, 1), "ms_per_step": round(total_ms / args.steps, 3), "launches": launches,
                "wall_ms_per_step": round(1e3 * wall / args.steps, 3),
-               "roofline": roofline(prec, rows_per_gpu * ny, T * args.steps, T * args.steps, total_ms, peak, peak_src)}
+               "roofline": roofline(prec, rows_per_gpu * ny, T * args.steps, T * args.steps, total_ms, peak, peak_src,
+                                    kernel="lbm::stream_collide_aa_kernel" if args.engine == "inplace" else "lbm::stream_collide_vec_kernel",
+                                    traffic_key=("none" if strong else "dp_inplace_large" if (args.engine == "inplace" and prec == "dp")
+                                                 else f"{prec}_8192x32768"))}
         res["reynolds"] = dl.gather_reynolds()
 
         # e2e: every rank uploads its slab from host memory, runs, downloads it again
@@ -400,13 +445,17 @@ def bench_multi(args):
                                         f"BASELINE configs[4]: weak scaling, {WEAK['nx_per_gpu']}x{ny} sites per GPU, DP (SP under 'sp'), {world} B200"),
                            "lattice": f"{nx}x{ny}", "timesteps_per_step": T, "scene": "channel walls + disc obstacle, tau 0.7, accel 0.005",
                            "parallelism": f"row slabs x{world}, halo rows stored peer-to-peer over NVLink ({args.transport}), boundary rows on a second stream",
+                           "engine": "in-place single buffer per slab (AA kernels)" if args.engine == "inplace" else "A/B double buffer per slab",
                            "l2": "tens of GB per GPU, far larger than L2"},
                 "roofline": dp["roofline"], "e2e": dp["e2e"], "gpu_launches": dp["launches"], "clocks": clocks,
                 "reynolds": dp["reynolds"], "achieved_gbs_per_gpu": dp["roofline"]["achieved"],
                 "wall_ms_per_step": dp["wall_ms_per_step"]}
         if "sp" in out:
             line["sp"] = {k: out["sp"][k] for k in ("value", "ms_per_step", "roofline", "e2e", "reynolds")}
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     dist.destroy_process_group()
     return 0
 
@@ -419,6 +468,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--transport", default="p2p", choices=["p2p", "staged"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--engine", default="ab", choices=["ab", "inplace"],
+                    help="N > 1 / strong workload: slab engine (N = 1 default workload measures both)")
     ap.add_argument("--workload", default="auto", choices=["auto", "weak", "strong"],
                     help="N > 1 only: weak = 8192x32768 per GPU (default), strong = 16384x65536 over all ranks")
     args = ap.parse_args()
@@ -426,6 +477,8 @@ def main():
         return reference_arm(args)
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
         return bench_multi(args)
+    if args.workload == "strong":
+        return bench_strong_single(args)
     if args.gpus > 1:
         raise SystemExit("bench.py: launch N > 1 with torchrun (one rank per GPU), e.g. python -m torch.distributed.run "
                          "--nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29500 bench.py --gpus N")

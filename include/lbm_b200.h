@@ -185,7 +185,10 @@ typedef struct {
 	                     is L2-resident, so HBM sees each site once per tb_depth steps instead of every step.
 	                     Possible because the in-place kernels have no write-after-read hazards: a row may take
 	                     step t as soon as rows i-1, i, i+1 have taken step t-1.  0 = off (one launch per step). */
-	int tb_rows;      /* band height H in rows; 0 = chosen so that (H + tb_depth) rows take ~40 MB */
+	int tb_rows;      /* band height H in rows; 0 = chosen so that (H + tb_depth) rows take ~45 MB (DP) / 60 MB (SP) */
+	int rows_per_thread; /* in-place kernels: >= 2 = each thread walks that many rows of its launch and loads the
+	                     populations of its next row before relaxing the current one (software pipelining against
+	                     L2 latency); 0/1 = one row per thread */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);

@@ -44,7 +44,8 @@ def _structs(real):
     class Tuning(ctypes.Structure):
         _fields_ = [("vec", ctypes.c_int), ("block", ctypes.c_int), ("neighbour", ctypes.c_int),
                     ("hints", ctypes.c_int), ("ctas_per_sm", ctypes.c_int), ("persistent", ctypes.c_int),
-                    ("pdl", ctypes.c_int), ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int)]
+                    ("pdl", ctypes.c_int), ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int),
+                    ("rows_per_thread", ctypes.c_int)]
 
     return Config, Scene, SlabInfo, Tuning
 
@@ -68,7 +69,8 @@ class Lib:
         if prec not in ("dp", "sp"):
             raise ValueError("prec must be 'dp' or 'sp'")
         self.prec = prec
-        self.path = os.path.join(HERE, f"liblbm_b200_{prec}.so")
+        # LBM_B200_LIBDIR: experiment builds of the SAME library (tools/ only); there is still no fallback
+        self.path = os.path.join(os.environ.get("LBM_B200_LIBDIR", HERE), f"liblbm_b200_{prec}.so")
         if not os.path.exists(self.path):
             raise ImportError(f"{self.path} is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
                               "(there is no CPU fallback)")

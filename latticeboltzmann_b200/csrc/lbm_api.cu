@@ -312,10 +312,13 @@ cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned
 
 /* in-place (AA) step kernels: phase 1 (from the reference layout) / phase 2 (back to it) */
 template <int V>
-cudaError_t launch_aa_v(int phase, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_aa_v(int phase, int pipe, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
 {
-	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1>, p, grid, block, st, pdl)
-	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2>, p, grid, block, st, pdl);
+	if (pipe)
+		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 1>, p, grid, block, st, pdl)
+		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 1>, p, grid, block, st, pdl);
+	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 0>, p, grid, block, st, pdl)
+	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 0>, p, grid, block, st, pdl);
 }
 
 template <int V>
@@ -363,6 +366,8 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			/* x: the vectors of one row; y: rows, capped (grid-stride) by ctas_per_sm and by the 65535 limit */
 			const unsigned gx = ((unsigned)(c->nyvec / V) + block - 1) / block;
 			unsigned gy = rows;
+			const int pipe = c->tune.rows_per_thread >= 2 && V <= 2;     /* wider vectors: the second register set spills */
+			if (pipe) gy = (rows + (unsigned)c->tune.rows_per_thread - 1) / (unsigned)c->tune.rows_per_thread;
 			if (c->tune.ctas_per_sm > 0) {
 				const unsigned cap = (unsigned)(sm_count(c->cfg.device) * c->tune.ctas_per_sm) / gx;
 				if (gy > cap) gy = cap < 1 ? 1 : cap;
@@ -370,11 +375,11 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			if (gy > 65535u) gy = 65535u;
 			const dim3 g2(gx, gy);
 			switch (V) {
-			case 1: e = launch_aa_v<1>(phase, p, g2, block, st, pdl); break;
-			case 2: e = launch_aa_v<2>(phase, p, g2, block, st, pdl); break;
-			case 4: e = launch_aa_v<4>(phase, p, g2, block, st, pdl); break;
+			case 1: e = launch_aa_v<1>(phase, pipe, p, g2, block, st, pdl); break;
+			case 2: e = launch_aa_v<2>(phase, pipe, p, g2, block, st, pdl); break;
+			case 4: e = launch_aa_v<4>(phase, pipe, p, g2, block, st, pdl); break;
 #ifdef LBM_FLOAT
-			case 8: e = launch_aa_v<8>(phase, p, g2, block, st, pdl); break;
+			case 8: e = launch_aa_v<8>(phase, pipe, p, g2, block, st, pdl); break;
 #endif
 			default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 			}
@@ -979,6 +984,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
 	if (n.tb_rows < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d", n.tb_rows);
+	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");
 	drop_graph(c);

@@ -481,33 +481,14 @@ template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(
 	}
 }
 
+// the nine populations the V sites (r, j0..j0+V-1) relax this step
 template <typename T, int V, int PHASE>
-__device__ __forceinline__ void update_vector_aa(const StepParams<T> &p, uint32_t rr, uint32_t jv, bool active, int tail_source)
+__device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T (&f)[9][V])
 {
-	int r = p.r0 + (int)rr;
-	if (r >= p.nxl) r -= p.nxl;                              // row ranges of the wavefront schedule may wrap (r1 > nxl)
-	const int j0 = p.jmin + (int)jv * V;
-	T *const own = p.dst + (size_t)(r + 1) * p.ldy;          // p.src == p.dst
-	T f[9][V], o[9][V];
-
+	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;    // p.src == p.dst
 	if constexpr (PHASE == 2) {
 #pragma unroll
 		for (int s = 0; s < 9; s++) ldc<V>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
-		relax_sites<T, V>(p, f, o, r, j0, tail_source);
-		if (active) {
-#pragma unroll
-			for (int s = 0; s < 9; s++) stv<0, V>(own + (size_t)s * p.plane + j0, o[s]);
-			if (r == 0) {                                    // as in the A/B kernel (LB.c:239,242,243)
-				stv<0, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
-				stv<0, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
-				stv<0, V>(p.dn_halo + 8 * p.dn_plane + j0, o[8]);
-			}
-			if (r == p.nxl - 1) {                            // (LB.c:237,240,241)
-				stv<0, V>(p.up_halo + 2 * p.up_plane + j0, o[2]);
-				stv<0, V>(p.up_halo + 5 * p.up_plane + j0, o[5]);
-				stv<0, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
-			}
-		}
 	} else {
 		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;          // LB.c:337-338
 		const int jr = j0 + V == p.ny ? 0 : j0 + V;
@@ -534,38 +515,102 @@ __device__ __forceinline__ void update_vector_aa(const StepParams<T> &p, uint32_
 				}
 			}
 		}
-		relax_sites<T, V>(p, f, o, r, j0, tail_source);
-		if (active) {
-			// slot k of site (x - e_k) receives o[opp(k)]; rows beyond the slab are the neighbour's owned boundary rows
-			T *srow[3];
-			size_t spl[3];
-			srow[1] = own;              spl[1] = p.plane;
-			if (r == 0) { srow[0] = p.dn_halo - p.ldy; spl[0] = p.dn_plane; } else { srow[0] = own - p.ldy; spl[0] = p.plane; }
-			if (r == p.nxl - 1) { srow[2] = p.up_halo + p.ldy; spl[2] = p.up_plane; } else { srow[2] = own + p.ldy; spl[2] = p.plane; }
-#pragma unroll
-			for (int k = 0; k < 9; k++) {
-				T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
-				if (pull_dj(k) == 0) stv<0, V>(b + j0, o[opposite(k)]);
-				else if (pull_dj(k) < 0) st_shifted<T, V, -1>(b, j0, jl, jr, o[opposite(k)]);
-				else st_shifted<T, V, 1>(b, j0, jl, jr, o[opposite(k)]);
-			}
-		}
 	}
 }
 
 template <typename T, int V, int PHASE>
-__global__ void __launch_bounds__(512)
+__device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, const T (&o)[9][V])
+{
+	T *const own = p.dst + (size_t)(r + 1) * p.ldy;
+	if constexpr (PHASE == 2) {
+#pragma unroll
+		for (int s = 0; s < 9; s++) stv<0, V>(own + (size_t)s * p.plane + j0, o[s]);
+		if (r == 0) {                                        // as in the A/B kernel (LB.c:239,242,243)
+			stv<0, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
+			stv<0, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
+			stv<0, V>(p.dn_halo + 8 * p.dn_plane + j0, o[8]);
+		}
+		if (r == p.nxl - 1) {                                // (LB.c:237,240,241)
+			stv<0, V>(p.up_halo + 2 * p.up_plane + j0, o[2]);
+			stv<0, V>(p.up_halo + 5 * p.up_plane + j0, o[5]);
+			stv<0, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
+		}
+	} else {
+		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
+		const int jr = j0 + V == p.ny ? 0 : j0 + V;
+		// slot k of site (x - e_k) receives o[opp(k)]; rows beyond the slab are the neighbour's owned boundary rows
+		T *srow[3];
+		size_t spl[3];
+		srow[1] = own;              spl[1] = p.plane;
+		if (r == 0) { srow[0] = p.dn_halo - p.ldy; spl[0] = p.dn_plane; } else { srow[0] = own - p.ldy; spl[0] = p.plane; }
+		if (r == p.nxl - 1) { srow[2] = p.up_halo + p.ldy; spl[2] = p.up_plane; } else { srow[2] = own + p.ldy; spl[2] = p.plane; }
+#pragma unroll
+		for (int k = 0; k < 9; k++) {
+			T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
+			if (pull_dj(k) == 0) stv<0, V>(b + j0, o[opposite(k)]);
+			else if (pull_dj(k) < 0) st_shifted<T, V, -1>(b, j0, jl, jr, o[opposite(k)]);
+			else st_shifted<T, V, 1>(b, j0, jl, jr, o[opposite(k)]);
+		}
+	}
+}
+
+// row ranges of the wavefront schedule may wrap (r1 > nxl)
+template <typename T> __device__ __forceinline__ int aa_row(const StepParams<T> &p, uint32_t rr)
+{
+	const int r = p.r0 + (int)rr;
+	return r >= p.nxl ? r - p.nxl : r;
+}
+
+// 2-D grid: x over the vectors of a row, y over rows -- no integer division per site.
+// PIPE == 0: one row per thread and pass (grid-stride over y).
+// PIPE == 1: each thread walks rows blockIdx.y, +gridDim.y, ... and loads the populations of its NEXT
+//            row before it relaxes the current one (two register sets, ping-pong), so the L2 latency
+//            of the loads is covered by ~300 instructions of arithmetic.  For the L2-resident runs
+//            (in-place small lattices, temporal blocking) that are bound by load latency at the
+//            occupancy 60-120 registers allow.  Safe in place: a site's nine slots are its own.
+#ifdef LBM_AA_MINB      /* experiment builds (tools/): 128-thread CTAs, at least LBM_AA_MINB of them per SM */
+#define LBM_AA_BOUNDS __launch_bounds__(128, LBM_AA_MINB)
+#else
+#define LBM_AA_BOUNDS __launch_bounds__(512)
+#endif
+template <typename T, int V, int PHASE, int PIPE>
+__global__ void LBM_AA_BOUNDS
 stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 {
-	// 2-D grid: x over the vectors of a row, y over rows (grid-stride) -- no integer division per site
 	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
 	const uint32_t rows = (uint32_t)(p.r1 - p.r0);
 	const uint32_t jv = blockIdx.x * blockDim.x + threadIdx.x;
+	const int j0 = p.jmin + (int)jv * V;
 	asm volatile("griddepcontrol.wait;" ::: "memory");
 	if (jv >= nvec) return;
-	for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y)
-		update_vector_aa<T, V, PHASE>(p, rr, jv, true, p.tail_source);
+	if constexpr (PIPE == 0) {
+		for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
+			const int r = aa_row(p, rr);
+			T f[9][V], o[9][V];
+			aa_load<T, V, PHASE>(p, r, j0, f);
+			relax_sites<T, V>(p, f, o, r, j0, p.tail_source);
+			aa_store<T, V, PHASE>(p, r, j0, o);
+		}
+	} else {
+		uint32_t rr = blockIdx.y;
+		if (rr >= rows) return;
+		const uint32_t st = gridDim.y;
+		T fa[9][V], fb[9][V], o[9][V];
+		aa_load<T, V, PHASE>(p, aa_row(p, rr), j0, fa);
+#pragma unroll 1
+		for (; rr < rows; rr += st) {
+			const int r = aa_row(p, rr);
+			const uint32_t nx = rr + st < rows ? rr + st : rr;       // last row: a harmless reload of its own (already consumed) slots
+			aa_load<T, V, PHASE>(p, aa_row(p, nx), j0, fb);
+			relax_sites<T, V>(p, fa, o, r, j0, p.tail_source);
+			aa_store<T, V, PHASE>(p, r, j0, o);
+#pragma unroll
+			for (int s = 0; s < 9; s++)
+#pragma unroll
+				for (int k = 0; k < V; k++) fa[s][k] = fb[s][k];
+		}
+	}
 }
 
 // ---------------------------------------------------------------------------

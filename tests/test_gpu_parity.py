@@ -52,7 +52,8 @@ ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), 
            "inplace": dict(inplace=1), "inplace+graph+pdl": dict(inplace=1, graph=4, pdl=1),
            # + temporal blocking in L2: bands of tb_rows rows advanced tb_depth steps each (wavefront schedule)
            "inplace+tb": dict(inplace=1, tb_depth=4, tb_rows=3),
-           "inplace+tb+graph+pdl": dict(inplace=1, tb_depth=6, tb_rows=5, graph=1, pdl=1)}
+           "inplace+tb+graph+pdl": dict(inplace=1, tb_depth=6, tb_rows=5, graph=1, pdl=1),
+           "inplace+tb+pipe": dict(inplace=1, tb_depth=8, tb_rows=12, rows_per_thread=3, vec=1, graph=1, pdl=1)}
 
 
 def _split(engine_kw):
@@ -160,6 +161,16 @@ def test_every_kernel_variant_is_bit_identical(prec):
                 lat.run(4)
                 lat.run(c["steps"] - 4)
                 _assert_same(lat.download("A"), o.f_view("A"), f"in-place fA with {tune}")
+        # software-pipelined in-place kernels (each thread walks rows_per_thread rows, loads one row ahead)
+        for v, rpt, extra in ((1, 2, {}), (1, 5, dict(tb_depth=4, tb_rows=9)), (2, 3, dict(pdl=1, graph=2)), (2, 96, {}),
+                              (1, 7, dict(ctas_per_sm=1, block=64)), (vecs[-1], 4, {})):
+            tune = dict(dict(vec=v, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=0, graph=0, tb_depth=0, tb_rows=0,
+                             rows_per_thread=rpt), **extra)
+            lat.set_tuning(**tune)
+            lat.upload(fA, walls)
+            lat.run(c["steps"])
+            _assert_same(lat.download("A"), o.f_view("A"), f"pipelined in-place fA with {tune}")
+        lat.set_tuning(rows_per_thread=0)
         # wavefront schedules: depth k, band height H (0 = automatic), with and without graph replay
         for k, h, g in ((2, 0, 0), (4, 7, 0), (8, 16, 1), (46, 3, 0), (10, 200, 1), (4, 1, 1), (6, 90, 0)):
             tune = dict(vec=vecs[-1], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=g, graph=g, tb_depth=k, tb_rows=h)
