@@ -194,6 +194,11 @@ int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
 /* Kernels launched by this context since creation (bench.py's gpu_launches). */
 long long lbm_kernel_launches(lbm_ctx *ctx);
+/* The launch list of ONE temporal-blocking macro-step for a single-slab ring of nx rows (host logic only, no
+ * GPU needed): launches[3n..3n+2] = (level, r0, r1), row range [r0,r1) with r1 > nx wrapping periodically;
+ * *depth_used = the depth after clamping to the ring (0: the lattice is too small, plain stepping is used).
+ * Returns the number of launches (which may exceed cap; only cap entries are written), -1 on bad arguments. */
+int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int *depth_used, int *launches, int cap);
 
 #ifdef __cplusplus
 }

@@ -58,7 +58,7 @@ SYMBOLS = [
     "lbm_compute_reynolds", "lbm_reynolds_column", "lbm_reynolds_from_column", "lbm_macroscopic",
     "lbm_print_lattice", "lbm_slab_info_get", "lbm_ipc_export", "lbm_ipc_connect", "lbm_connect_local",
     "lbm_group_run", "lbm_halo_pack", "lbm_halo_unpack", "lbm_step_rows", "lbm_stream_handle",
-    "lbm_stream_join", "lbm_set_tuning", "lbm_get_tuning", "lbm_kernel_launches",
+    "lbm_stream_join", "lbm_set_tuning", "lbm_get_tuning", "lbm_kernel_launches", "lbm_tb_schedule",
 ]
 
 
@@ -87,6 +87,8 @@ class Lib:
         d.lbm_kernel_launches.restype = ctypes.c_longlong
         d.lbm_kernel_launches.argtypes = [vp]
         d.lbm_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(self.Config)]
+        d.lbm_tb_schedule.restype = ci
+        d.lbm_tb_schedule.argtypes = [ci, ci, ci, ci, ctypes.POINTER(ci), vp, ci]
         for name, args in {
             "lbm_destroy": [vp], "lbm_initialize_arrays": [vp, ctypes.POINTER(self.Scene)],
             "lbm_upload": [vp, vp, vp, vp, ci], "lbm_download": [vp, vp, vp, vp, ci],

@@ -256,7 +256,10 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		const double row_bytes = 9.0 * c->ldy * sizeof(real_t);
 		const int k = sizeof(real_t) == 8 ? 16 : 8;
 		const double band = sizeof(real_t) == 8 ? 45e6 : 60e6;
-		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) c->tune.tb_depth = k;
+		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) {
+			c->tune.tb_depth = k;
+			if (sizeof(real_t) == 4) c->tune.vec = 2;                /* SP 800x4000: 98.7 (vec 2) vs 83.8 GLUPS (vec 4), profiles/r01_run11 */
+		}
 	}
 	*out = c;
 	return LBM_OK;
@@ -541,45 +544,61 @@ int enqueue_step(lbm_ctx *c, int src, int tail_source)
 // HBM traffic per site update drops from 18 reals to ~18/k.  Results are bit-identical: the same
 // kernels do the same arithmetic on the same values, only the order of independent work changes.
 // ---------------------------------------------------------------------------
-int enqueue_macro(lbm_ctx *c, int t0, int k, int H0, int H, int nsteps)
+struct TbPlan { int k, H0, H; };
+
+/* depth and band heights actually used for a ring of nx rows (k == 0: no temporal blocking possible) */
+TbPlan tb_plan(int nx, int ldy, int tb_depth, int tb_rows)
+{
+	TbPlan pl = {tb_depth & ~1, 0, tb_rows};
+	while (pl.k >= 2 && 2 * pl.k + 2 > nx) pl.k -= 2;            /* pyramid base H0 >= 2k inside the ring */
+	if (pl.k < 2) { pl.k = 0; return pl; }
+	if (pl.H <= 0) {                                             /* (H + k) rows ~ 45 MB (DP) / 60 MB (SP): measured best, profiles/r01_run9,10 */
+		const double row_bytes = 9.0 * ldy * sizeof(real_t);
+		pl.H = (int)((sizeof(real_t) == 8 ? 45e6 : 60e6) / row_bytes) - pl.k;
+	}
+	if (pl.H < 2) pl.H = 2;
+	pl.H0 = pl.H < 2 * pl.k ? 2 * pl.k : pl.H;
+	if (pl.H0 > nx - 1) pl.H0 = nx - 1;
+	if (nx - pl.H0 > 0) {                                        /* equal bands over [H0, nx) instead of a short last one */
+		const int nb = (nx - pl.H0 + pl.H - 1) / pl.H;
+		pl.H = (nx - pl.H0 + nb - 1) / nb;
+		if (pl.H < 2) pl.H = 2;
+	}
+	return pl;
+}
+
+/* the launches of one macro-step of kk <= pl.k levels, in order: visit(level, r0, r1), r1 may exceed nx (wraps) */
+template <typename F> int tb_for_each_launch(int nx, const TbPlan &pl, int kk, F visit)
 {
 	int rc;
-	const int nx = c->nxl;
-	for (int s = 0; s < k; s++)
-		if ((rc = launch_step(c, (t0 + s) & 1, s, H0 - s, t0 + s != nsteps - 1, c->stream[0]))) return rc;
-	for (int a = H0; a < nx; a += H) {
-		const int b = a + H < nx ? a + H : nx;
-		for (int s = 0; s < k; s++)
-			if ((rc = launch_step(c, (t0 + s) & 1, a - s, b - s, t0 + s != nsteps - 1, c->stream[0]))) return rc;
+	for (int s = 0; s < kk; s++)
+		if ((rc = visit(s, s, pl.H0 - s))) return rc;
+	for (int a = pl.H0; a < nx; a += pl.H) {
+		const int b = a + pl.H < nx ? a + pl.H : nx;
+		for (int s = 0; s < kk; s++)
+			if ((rc = visit(s, a - s, b - s))) return rc;
 	}
-	for (int s = 1; s < k; s++)
-		if ((rc = launch_step(c, (t0 + s) & 1, nx - s, nx + s, t0 + s != nsteps - 1, c->stream[0]))) return rc;
-	return LBM_OK;
+	for (int s = 1; s < kk; s++)
+		if ((rc = visit(s, nx - s, nx + s))) return rc;
+	return 0;
+}
+
+int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
+{
+	return tb_for_each_launch(c->nxl, pl, kk, [&](int s, int r0, int r1) {
+		return launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0]);
+	});
 }
 
 int run_wavefront(lbm_ctx *c, int nsteps)
 {
 	int rc;
-	int k = c->tune.tb_depth & ~1;
-	const int nx = c->nxl;
-	while (k >= 2 && 2 * k + 2 > nx) k -= 2;                     /* pyramid base H0 >= 2k inside the ring */
+	const TbPlan pl = tb_plan(c->nxl, c->ldy, c->tune.tb_depth, c->tune.tb_rows);
+	const int k = pl.k, H = pl.H;
 	if (k < 2) {
 		for (int t = 0; t < nsteps; t++)
 			if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
 		return LBM_OK;
-	}
-	int H = c->tune.tb_rows;
-	if (H <= 0) {                                                /* (H + k) rows ~ 45 MB (DP) / 60 MB (SP): measured best, profiles/r01_run9 */
-		const double row_bytes = 9.0 * c->ldy * sizeof(real_t);
-		H = (int)((sizeof(real_t) == 8 ? 45e6 : 60e6) / row_bytes) - k;
-	}
-	if (H < 2) H = 2;
-	int H0 = H < 2 * k ? 2 * k : H;
-	if (H0 > nx - 1) H0 = nx - 1;
-	if (nx - H0 > 0) {                                           /* equal bands over [H0, nx) instead of a short last one */
-		const int nb = (nx - H0 + H - 1) / H;
-		H = (nx - H0 + nb - 1) / nb;
-		if (H < 2) H = 2;
 	}
 	int t = 0;
 	if (c->tune.graph > 0 && nsteps - k >= k) {
@@ -588,7 +607,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 			cudaGraph_t g = nullptr;
 			CK(cudaStreamBeginCapture(c->stream[0], cudaStreamCaptureModeThreadLocal));
 			const long long l0 = c->launches;
-			rc = enqueue_macro(c, 0, k, H0, H, 1 << 30);         /* every level with its tail source */
+			rc = enqueue_macro(c, 0, k, pl, 1 << 30);            /* every level with its tail source */
 			c->wf_launches = c->launches - l0;
 			c->launches = l0;
 			cudaError_t e = cudaStreamEndCapture(c->stream[0], &g);
@@ -606,7 +625,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 	}
 	while (t < nsteps) {
 		const int kk = nsteps - t < k ? nsteps - t : k;          /* even; H0 >= 2k >= 2kk */
-		if ((rc = enqueue_macro(c, t, kk, H0, H, nsteps))) return rc;
+		if ((rc = enqueue_macro(c, t, kk, pl, nsteps))) return rc;
 		t += kk;
 	}
 	return LBM_OK;
@@ -998,6 +1017,23 @@ int lbm_get_tuning(lbm_ctx *c, lbm_tuning *t)
 	return LBM_OK;
 }
 long long lbm_kernel_launches(lbm_ctx *c) { return c ? c->launches : 0; }
+
+int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int *depth_used, int *launches, int cap)
+{
+	if (nx < 1 || ny < 2 || tb_depth < 0 || tb_rows < 0 || (cap > 0 && !launches)) { fail(LBM_ERR_ARG, "lbm_tb_schedule: bad argument"); return -1; }
+	const int per128 = 128 / (int)sizeof(real_t);
+	const int ldy = ((ny + per128 - 1) / per128) * per128;
+	const TbPlan pl = tb_plan(nx, ldy, tb_depth, tb_rows);
+	if (depth_used) *depth_used = pl.k;
+	if (pl.k < 2) return 0;
+	int n = 0;
+	tb_for_each_launch(nx, pl, pl.k, [&](int s, int r0, int r1) {
+		if (n < cap) { launches[3 * n] = s; launches[3 * n + 1] = r0; launches[3 * n + 2] = r1; }
+		n++;
+		return 0;
+	});
+	return n;
+}
 
 } // extern "C"
 
