@@ -186,6 +186,9 @@ typedef struct {
 	                     Possible because the in-place kernels have no write-after-read hazards: a row may take
 	                     step t as soon as rows i-1, i, i+1 have taken step t-1.  0 = off (one launch per step). */
 	int tb_rows;      /* band height H in rows; 0 = chosen so that (H + tb_depth) rows take ~45 MB (DP) / 60 MB (SP) */
+	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
+	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 32 KB
+	                     row segments only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
 	int rows_per_thread; /* in-place kernels: >= 2 = each thread walks that many rows of its launch and loads the
 	                     populations of its next row before relaxing the current one (software pipelining against
 	                     L2 latency); 0/1 = one row per thread */
@@ -194,11 +197,12 @@ int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
 /* Kernels launched by this context since creation (bench.py's gpu_launches). */
 long long lbm_kernel_launches(lbm_ctx *ctx);
-/* The launch list of ONE temporal-blocking macro-step for a single-slab ring of nx rows (host logic only, no
- * GPU needed): launches[3n..3n+2] = (level, r0, r1), row range [r0,r1) with r1 > nx wrapping periodically;
- * *depth_used = the depth after clamping to the ring (0: the lattice is too small, plain stepping is used).
- * Returns the number of launches (which may exceed cap; only cap entries are written), -1 on bad arguments. */
-int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int *depth_used, int *launches, int cap);
+/* The launch list of ONE temporal-blocking macro-step for a single-slab ring of nx rows x ny columns (host logic
+ * only, no GPU needed): launches[5n..5n+4] = (level, r0, r1, j0, j1): rows [r0,r1) and columns [j0,j1), either
+ * range may run past nx / ny and then wraps periodically; j0 == j1 == 0 means whole rows.  *depth_used = the depth
+ * after clamping to the ring (0: the lattice is too small, plain stepping is used).  Returns the number of
+ * launches (which may exceed cap; only cap entries are written), -1 on bad arguments. */
+int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
 
 #ifdef __cplusplus
 }

@@ -45,7 +45,7 @@ def _structs(real):
         _fields_ = [("vec", ctypes.c_int), ("block", ctypes.c_int), ("neighbour", ctypes.c_int),
                     ("hints", ctypes.c_int), ("ctas_per_sm", ctypes.c_int), ("persistent", ctypes.c_int),
                     ("pdl", ctypes.c_int), ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int),
-                    ("rows_per_thread", ctypes.c_int)]
+                    ("tb_cols", ctypes.c_int), ("rows_per_thread", ctypes.c_int)]
 
     return Config, Scene, SlabInfo, Tuning
 
@@ -88,7 +88,7 @@ class Lib:
         d.lbm_kernel_launches.argtypes = [vp]
         d.lbm_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(self.Config)]
         d.lbm_tb_schedule.restype = ci
-        d.lbm_tb_schedule.argtypes = [ci, ci, ci, ci, ctypes.POINTER(ci), vp, ci]
+        d.lbm_tb_schedule.argtypes = [ci, ci, ci, ci, ci, ctypes.POINTER(ci), vp, ci]
         for name, args in {
             "lbm_destroy": [vp], "lbm_initialize_arrays": [vp, ctypes.POINTER(self.Scene)],
             "lbm_upload": [vp, vp, vp, vp, ci], "lbm_download": [vp, vp, vp, vp, ci],

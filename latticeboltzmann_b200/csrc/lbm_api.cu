@@ -88,7 +88,6 @@ struct lbm_ctx {
 	cudaGraphExec_t graph_exec;  // captured `graph_pairs` x (A->B, B->A) steps with the current tuning
 	int graph_pairs;
 	cudaGraphExec_t wf_exec;     // captured wavefront macro-step (wf_k timesteps, bands of wf_h rows)
-	int wf_k, wf_h;
 	long long wf_launches;       // kernels in that graph
 };
 
@@ -112,7 +111,6 @@ void drop_graph(lbm_ctx *c)
 	c->graph_pairs = 0;
 	if (c->wf_exec) cudaGraphExecDestroy(c->wf_exec);
 	c->wf_exec = nullptr;
-	c->wf_k = c->wf_h = 0;
 }
 
 int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_OK; }
@@ -345,12 +343,20 @@ int sm_count(int device)
 
 // One pull step src -> src^1 over owned rows [r0,r1): vector kernel for j < NYVECMAX,
 // scalar-order kernel for the ragged tail (LB.c:195-196) or for everything (LB.c:198).
-int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st)
+// jc0 < jc1: restrict the launch to columns [jc0, jc1) (multiples of 8, jc1 may exceed ny and wraps) -- only the
+// in-place vector kernel takes a column range (2-D temporal blocking; needs nyvec == ny)
+int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st, int jc0 = 0, int jc1 = 0)
 {
 	if (r1 <= r0) return LBM_OK;
 	StepParams<real_t> p = make_params(c, src, r0, r1, tail_source);
 	const unsigned rows = (unsigned)(r1 - r0);
 	int jtail = 0;
+	unsigned ncols = (unsigned)c->nyvec;
+	if (jc1 > jc0) {
+		if (!c->inplace || c->nyvec != c->ny || c->vw <= 1) return fail(LBM_ERR_STATE, "launch_step: column ranges need the in-place vector kernel");
+		p.jmin = jc0; p.jmax = jc1;
+		ncols = (unsigned)(jc1 - jc0);
+	}
 	if (c->vw > 1 && c->nyvec > 0) {
 		int V = c->tune.vec;
 		if (V > c->vw) V = c->vw;
@@ -367,7 +373,7 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		if (c->inplace) {
 			const int phase = src == 0 ? 1 : 2;
 			/* x: the vectors of one row; y: rows, capped (grid-stride) by ctas_per_sm and by the 65535 limit */
-			const unsigned gx = ((unsigned)(c->nyvec / V) + block - 1) / block;
+			const unsigned gx = (ncols / (unsigned)V + block - 1) / block;
 			unsigned gy = rows;
 			const int pipe = c->tune.rows_per_thread >= 2 && V <= 2;     /* wider vectors: the second register set spills */
 			if (pipe) gy = (rows + (unsigned)c->tune.rows_per_thread - 1) / (unsigned)c->tune.rows_per_thread;
@@ -544,57 +550,102 @@ int enqueue_step(lbm_ctx *c, int src, int tail_source)
 // HBM traffic per site update drops from 18 reals to ~18/k.  Results are bit-identical: the same
 // kernels do the same arithmetic on the same values, only the order of independent work changes.
 // ---------------------------------------------------------------------------
-struct TbPlan { int k, H0, H; };
+// One dimension of the schedule: a periodic axis of n cells cut into pieces whose extent at level s is
+//   pyramid [a + g s, b - g s) | parallelogram [a - g s, b - g s) | inverted pyramid [n - g s, n + g s) | whole axis
+// g = cells the piece boundaries move per level (>= the stencil reach 1; 8 along j keeps vectors aligned).
+struct TbPiece { int type, a, b; };
+enum { TB_PYRAMID = 0, TB_PARALLELOGRAM = 1, TB_INVERTED = 2, TB_WHOLE = 3 };
+struct TbAxis { int n, g, npieces; TbPiece piece[1026]; };
+struct TbPlan { int k; TbAxis rows, cols; };
 
-/* depth and band heights actually used for a ring of nx rows (k == 0: no temporal blocking possible) */
-TbPlan tb_plan(int nx, int ldy, int tb_depth, int tb_rows)
+inline void tb_range(const TbAxis &ax, const TbPiece &pc, int s, int *lo, int *hi)
 {
-	TbPlan pl = {tb_depth & ~1, 0, tb_rows};
-	while (pl.k >= 2 && 2 * pl.k + 2 > nx) pl.k -= 2;            /* pyramid base H0 >= 2k inside the ring */
-	if (pl.k < 2) { pl.k = 0; return pl; }
-	if (pl.H <= 0) {                                             /* (H + k) rows ~ 45 MB (DP) / 60 MB (SP): measured best, profiles/r01_run9,10 */
-		const double row_bytes = 9.0 * ldy * sizeof(real_t);
-		pl.H = (int)((sizeof(real_t) == 8 ? 45e6 : 60e6) / row_bytes) - pl.k;
+	switch (pc.type) {
+	case TB_PYRAMID: *lo = pc.a + ax.g * s; *hi = pc.b - ax.g * s; break;
+	case TB_PARALLELOGRAM: *lo = pc.a - ax.g * s; *hi = pc.b - ax.g * s; break;
+	case TB_INVERTED: *lo = ax.n - ax.g * s; *hi = ax.n + ax.g * s; break;
+	default: *lo = 0; *hi = ax.n; break;
 	}
-	if (pl.H < 2) pl.H = 2;
-	pl.H0 = pl.H < 2 * pl.k ? 2 * pl.k : pl.H;
-	if (pl.H0 > nx - 1) pl.H0 = nx - 1;
-	if (nx - pl.H0 > 0) {                                        /* equal bands over [H0, nx) instead of a short last one */
-		const int nb = (nx - pl.H0 + pl.H - 1) / pl.H;
-		pl.H = (nx - pl.H0 + nb - 1) / nb;
-		if (pl.H < 2) pl.H = 2;
-	}
-	return pl;
 }
 
-/* the launches of one macro-step of kk <= pl.k levels, in order: visit(level, r0, r1), r1 may exceed nx (wraps) */
-template <typename F> int tb_for_each_launch(int nx, const TbPlan &pl, int kk, F visit)
+/* pieces of one axis: pyramid base P0 >= 2 g k, then equal parallelograms of ~P cells, then the inverted pyramid */
+void tb_axis(TbAxis *ax, int n, int g, int k, int P)
+{
+	ax->n = n; ax->g = g; ax->npieces = 0;
+	if (P < 2 * g) P = 2 * g;
+	int P0 = P < 2 * g * k ? 2 * g * k : P;
+	if (P0 > n - g) P0 = n - g;
+	P0 = P0 / g * g;
+	ax->piece[ax->npieces++] = TbPiece{TB_PYRAMID, 0, P0};
+	if (n - P0 > 0) {
+		int nb = (n - P0 + P - 1) / P;
+		if (nb > 1023) nb = 1023;
+		int Pe = ((n - P0 + nb - 1) / nb + g - 1) / g * g;       /* equal pieces instead of a short last one */
+		for (int a = P0; a < n; a += Pe) ax->piece[ax->npieces++] = TbPiece{TB_PARALLELOGRAM, a, a + Pe < n ? a + Pe : n};
+	}
+	ax->piece[ax->npieces++] = TbPiece{TB_INVERTED, 0, 0};
+}
+
+/* depth, row bands and column strips actually used for a ring of nx rows x ny columns (k == 0: plain stepping).
+ * tb_cols: 0 = automatic (strips only where full-width bands would be lower than 64 rows), >= ny = full width */
+void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int tb_depth, int tb_rows, int tb_cols)
+{
+	const int G = 8;                                             /* column skew per level: keeps every vector width aligned */
+	int k = tb_depth & ~1;
+	while (k >= 2 && 2 * k + 2 > nx) k -= 2;                     /* pyramid base >= 2k inside the ring */
+	pl->k = k < 2 ? 0 : k;
+	if (!pl->k) return;
+	const double budget = sizeof(real_t) == 8 ? 45e6 : 60e6;     /* bytes of a tile incl. its skew margin: measured best, profiles/r01_run9,10 */
+	const double cell = 9.0 * sizeof(real_t);
+	int W = tb_cols;
+	if (!strips_ok || ny % G || 2 * G * k + G > ny) W = ny;      /* strips need aligned, wide enough rows */
+	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)(32768 / sizeof(real_t));   /* 32 KB row segments */
+	if (W >= ny) {
+		pl->cols.n = ny; pl->cols.g = G; pl->cols.npieces = 1;
+		pl->cols.piece[0] = TbPiece{TB_WHOLE, 0, ny};
+		W = ldy;
+	} else {
+		W = (W + G - 1) / G * G;
+		tb_axis(&pl->cols, ny, G, k, W);
+		W += G * k;
+	}
+	int H = tb_rows;
+	if (H <= 0) H = (int)(budget / (cell * W)) - k;
+	tb_axis(&pl->rows, nx, 1, k, H < 2 ? 2 : H);
+}
+
+/* the launches of one macro-step of kk <= pl.k levels, in order: visit(level, r0, r1, j0, j1); r1 / j1 may exceed
+ * nx / ny (the range wraps); j0 == j1 == 0 means whole rows.  Column pieces outermost, row pieces next, levels
+ * innermost: valid because each axis' piece order is (1-D argument in DESIGN.md) and the tile is their product. */
+template <typename F> int tb_for_each_launch(const TbPlan &pl, int kk, F visit)
 {
 	int rc;
-	for (int s = 0; s < kk; s++)
-		if ((rc = visit(s, s, pl.H0 - s))) return rc;
-	for (int a = pl.H0; a < nx; a += pl.H) {
-		const int b = a + pl.H < nx ? a + pl.H : nx;
-		for (int s = 0; s < kk; s++)
-			if ((rc = visit(s, a - s, b - s))) return rc;
-	}
-	for (int s = 1; s < kk; s++)
-		if ((rc = visit(s, nx - s, nx + s))) return rc;
+	for (int ci = 0; ci < pl.cols.npieces; ci++)
+		for (int ri = 0; ri < pl.rows.npieces; ri++)
+			for (int s = 0; s < kk; s++) {
+				int r0, r1, j0, j1;
+				tb_range(pl.rows, pl.rows.piece[ri], s, &r0, &r1);
+				tb_range(pl.cols, pl.cols.piece[ci], s, &j0, &j1);
+				if (r1 <= r0 || j1 <= j0) continue;                  /* inverted pyramids are empty at level 0 */
+				if (pl.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
+				if ((rc = visit(s, r0, r1, j0, j1))) return rc;
+			}
 	return 0;
 }
 
 int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 {
-	return tb_for_each_launch(c->nxl, pl, kk, [&](int s, int r0, int r1) {
-		return launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0]);
+	return tb_for_each_launch(pl, kk, [&](int s, int r0, int r1, int j0, int j1) {
+		return launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1);
 	});
 }
 
 int run_wavefront(lbm_ctx *c, int nsteps)
 {
 	int rc;
-	const TbPlan pl = tb_plan(c->nxl, c->ldy, c->tune.tb_depth, c->tune.tb_rows);
-	const int k = pl.k, H = pl.H;
+	static thread_local TbPlan pl;                               /* ~25 KB: not on the stack of every call */
+	tb_plan(&pl, c->nxl, c->ny, c->ldy, c->inplace && c->vw > 1 && c->nyvec == c->ny, c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
+	const int k = pl.k;
 	if (k < 2) {
 		for (int t = 0; t < nsteps; t++)
 			if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
@@ -602,8 +653,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 	}
 	int t = 0;
 	if (c->tune.graph > 0 && nsteps - k >= k) {
-		if (!c->wf_exec || c->wf_k != k || c->wf_h != H) {
-			drop_graph(c);
+		if (!c->wf_exec) {                                       /* any change of tuning drops the graph */
 			cudaGraph_t g = nullptr;
 			CK(cudaStreamBeginCapture(c->stream[0], cudaStreamCaptureModeThreadLocal));
 			const long long l0 = c->launches;
@@ -616,7 +666,6 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 			e = cudaGraphInstantiate(&c->wf_exec, g, 0);
 			cudaGraphDestroy(g);
 			CK(e);
-			c->wf_k = k; c->wf_h = H;
 		}
 		for (; nsteps - k - t >= k; t += k) {                    /* keep the last macro-step out: its last level leaves A un-sourced */
 			CK(cudaGraphLaunch(c->wf_exec, c->stream[0]));
@@ -624,7 +673,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 		}
 	}
 	while (t < nsteps) {
-		const int kk = nsteps - t < k ? nsteps - t : k;          /* even; H0 >= 2k >= 2kk */
+		const int kk = nsteps - t < k ? nsteps - t : k;          /* even; pyramid bases >= 2k >= 2kk */
 		if ((rc = enqueue_macro(c, t, kk, pl, nsteps))) return rc;
 		t += kk;
 	}
@@ -1002,7 +1051,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
-	if (n.tb_rows < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d", n.tb_rows);
+	if (n.tb_rows < 0 || n.tb_cols < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d, tb_cols %d", n.tb_rows, n.tb_cols);
 	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");
@@ -1018,17 +1067,18 @@ int lbm_get_tuning(lbm_ctx *c, lbm_tuning *t)
 }
 long long lbm_kernel_launches(lbm_ctx *c) { return c ? c->launches : 0; }
 
-int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int *depth_used, int *launches, int cap)
+int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap)
 {
-	if (nx < 1 || ny < 2 || tb_depth < 0 || tb_rows < 0 || (cap > 0 && !launches)) { fail(LBM_ERR_ARG, "lbm_tb_schedule: bad argument"); return -1; }
+	if (nx < 1 || ny < 2 || tb_depth < 0 || tb_rows < 0 || tb_cols < 0 || (cap > 0 && !launches)) { fail(LBM_ERR_ARG, "lbm_tb_schedule: bad argument"); return -1; }
 	const int per128 = 128 / (int)sizeof(real_t);
 	const int ldy = ((ny + per128 - 1) / per128) * per128;
-	const TbPlan pl = tb_plan(nx, ldy, tb_depth, tb_rows);
+	static thread_local TbPlan pl;
+	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, tb_depth, tb_rows, tb_cols);
 	if (depth_used) *depth_used = pl.k;
 	if (pl.k < 2) return 0;
 	int n = 0;
-	tb_for_each_launch(nx, pl, pl.k, [&](int s, int r0, int r1) {
-		if (n < cap) { launches[3 * n] = s; launches[3 * n + 1] = r0; launches[3 * n + 2] = r1; }
+	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1) {
+		if (n < cap) { int *o = launches + 5 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; }
 		n++;
 		return 0;
 	});

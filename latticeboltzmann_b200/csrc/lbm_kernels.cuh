@@ -581,7 +581,8 @@ stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
 	const uint32_t rows = (uint32_t)(p.r1 - p.r0);
 	const uint32_t jv = blockIdx.x * blockDim.x + threadIdx.x;
-	const int j0 = p.jmin + (int)jv * V;
+	int j0 = p.jmin + (int)jv * V;
+	if (j0 >= p.ny) j0 -= p.ny;                              // column ranges of the 2-D wavefront schedule may wrap (jmax > ny)
 	asm volatile("griddepcontrol.wait;" ::: "memory");
 	if (jv >= nvec) return;
 	if constexpr (PIPE == 0) {

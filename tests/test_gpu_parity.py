@@ -53,7 +53,9 @@ ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), 
            # + temporal blocking in L2: bands of tb_rows rows advanced tb_depth steps each (wavefront schedule)
            "inplace+tb": dict(inplace=1, tb_depth=4, tb_rows=3),
            "inplace+tb+graph+pdl": dict(inplace=1, tb_depth=6, tb_rows=5, graph=1, pdl=1),
-           "inplace+tb+pipe": dict(inplace=1, tb_depth=8, tb_rows=12, rows_per_thread=3, vec=1, graph=1, pdl=1)}
+           "inplace+tb+pipe": dict(inplace=1, tb_depth=8, tb_rows=12, rows_per_thread=3, vec=1, graph=1, pdl=1),
+           # 2-D tiles: column strips as well as row bands (falls back to bands where ny is not a multiple of 8)
+           "inplace+tb2d": dict(inplace=1, tb_depth=4, tb_rows=16, tb_cols=256, graph=1, pdl=1)}
 
 
 def _split(engine_kw):
@@ -172,8 +174,10 @@ def test_every_kernel_variant_is_bit_identical(prec):
             _assert_same(lat.download("A"), o.f_view("A"), f"pipelined in-place fA with {tune}")
         lat.set_tuning(rows_per_thread=0)
         # wavefront schedules: depth k, band height H (0 = automatic), with and without graph replay
-        for k, h, g in ((2, 0, 0), (4, 7, 0), (8, 16, 1), (46, 3, 0), (10, 200, 1), (4, 1, 1), (6, 90, 0)):
-            tune = dict(vec=vecs[-1], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=g, graph=g, tb_depth=k, tb_rows=h)
+        for k, h, g, w in ((2, 0, 0, 0), (4, 7, 0, 0), (8, 16, 1, 0), (46, 3, 0, 0), (10, 200, 1, 0), (4, 1, 1, 0), (6, 90, 0, 0),
+                           (4, 20, 0, 128), (6, 0, 1, 104), (2, 7, 0, 64), (8, 30, 1, 8), (16, 40, 0, 200), (2, 95, 1, 256)):
+            tune = dict(vec=vecs[-1] if w == 0 else vecs[(k // 2) % len(vecs)], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0,
+                        pdl=g, graph=g, tb_depth=k, tb_rows=h, tb_cols=w)
             lat.set_tuning(**tune)
             lat.upload(fA, walls)
             lat.run(c["steps"])

@@ -1,23 +1,45 @@
 """CPU: the temporal-blocking (wavefront) schedule of the in-place engine is a valid order.
 
-The in-place kernels have read-after-write dependencies only (DESIGN.md "Temporal blocking"): row i may
-take level s once rows i-1, i, i+1 (periodic) have taken level s-1.  lbm_tb_schedule returns the launch
-list the library really enqueues (host logic, no GPU); this test replays it on a row-level model and
-checks every dependency, full coverage and the band sizes."""
+The in-place kernels have read-after-write dependencies only (DESIGN.md "Temporal blocking"): site (i, j)
+may take level s once its 3x3 neighbourhood (periodic in both axes) has taken level s-1.  lbm_tb_schedule
+returns the launch list the library really enqueues (host logic, no GPU); this test replays it on a
+site-level model and checks every dependency, full coverage and the tile sizes."""
 import numpy as np
 import pytest
 
 from latticeboltzmann_b200.solver import tb_schedule
 
-CASES = [(400, 4000, 16, 0), (400, 4000, 8, 148), (800, 4000, 12, 196), (96, 520, 46, 3), (96, 520, 4, 1), (11, 64, 4, 2),
-         (10, 64, 4, 0), (7, 40, 2, 0), (6, 40, 2, 5), (5, 40, 2, 0), (3, 40, 2, 0), (8192, 32768, 4, 15), (401, 1000, 32, 37),
-         (64, 64, 30, 2), (66, 64, 32, 2), (1000, 256, 1024, 0)]
+#        nx    ny   depth rows cols
+CASES = [(400, 4000, 16, 0, 0), (400, 4000, 8, 148, 0), (800, 4000, 12, 196, 0), (96, 520, 46, 3, 0), (96, 520, 4, 1, 0),
+         (11, 64, 4, 2, 0), (10, 64, 4, 0, 0), (7, 40, 2, 0, 0), (6, 40, 2, 5, 0), (5, 40, 2, 0, 0), (3, 40, 2, 0, 0),
+         (401, 1000, 32, 37, 0), (64, 64, 30, 2, 0), (66, 64, 32, 2, 0), (1000, 256, 1024, 0, 0),
+         # column strips as well (2-D tiles)
+         (96, 520, 4, 20, 128), (96, 520, 6, 0, 104), (40, 1024, 8, 12, 256), (200, 2048, 16, 50, 512), (33, 136, 4, 9, 64),
+         (24, 144, 8, 5, 16), (64, 4096, 4, 16, 0), (50, 264, 16, 10, 8)]
+
+
+def _check(nx, ny, k, launches):
+    level = np.zeros((nx, ny), dtype=np.int16)          # levels completed per site
+    for s, r0, r1, j0, j1 in launches:
+        if j0 == j1 == 0:
+            j1 = ny
+        assert 0 <= s < k and 0 <= r0 < r1 <= r0 + nx and r0 < nx and 0 <= j0 < j1 <= j0 + ny and j0 < ny
+        assert j0 % 8 == 0 and (j1 % 8 == 0 or j1 == ny)
+        rows, cols = np.arange(r0, r1) % nx, np.arange(j0, j1) % ny
+        mine = level[np.ix_(rows, cols)]
+        assert (mine == s).all(), f"level {s} rows [{r0},{r1}) cols [{j0},{j1}) taken twice or out of order"
+        for di in (-1, 0, 1):                           # RAW: the 3x3 neighbourhood's previous level is done
+            for dj in (-1, 0, 1):
+                nb = level[np.ix_((rows + di) % nx, (cols + dj) % ny)]
+                assert (nb >= s).all(), f"level {s} rows [{r0},{r1}) cols [{j0},{j1}): neighbour ({di:+d},{dj:+d}) behind"
+        level[np.ix_(rows, cols)] = s + 1
+    assert (level == k).all()                           # every site took every level exactly once
 
 
 @pytest.mark.parametrize("prec", ["dp", "sp"])
-@pytest.mark.parametrize("nx,ny,depth,rows", CASES)
-def test_wavefront_schedule_respects_dependencies(nx, ny, depth, rows, prec):
-    k, launches = tb_schedule(nx, ny, depth, rows, prec)
+@pytest.mark.parametrize("nx,ny,depth,rows,cols", CASES)
+def test_wavefront_schedule_respects_dependencies(nx, ny, depth, rows, cols, prec):
+    k, launches = tb_schedule(nx, ny, depth, rows, cols, prec)
     if 2 * (depth & ~1) + 2 > nx:                       # ring too small for that depth: clamped, possibly to none
         assert k < depth and (k == 0 or 2 * k + 2 <= nx)
     else:
@@ -25,21 +47,27 @@ def test_wavefront_schedule_respects_dependencies(nx, ny, depth, rows, prec):
     if k == 0:
         assert launches == []
         return
-    level = np.zeros(nx, dtype=np.int64)                # levels completed per row
-    for s, r0, r1 in launches:
-        assert 0 <= s < k and 0 <= r0 < r1 <= r0 + nx and r0 < nx
-        rows_ = np.arange(r0, r1) % nx
-        assert len(set(rows_.tolist())) == len(rows_)
-        for d in (-1, 0, 1):                            # RAW: the neighbours' previous level is done (and nothing is skipped)
-            assert (level[(rows_ + d) % nx] >= s).all(), f"level {s} rows [{r0},{r1}): neighbour {d:+d} not at level {s}"
-        assert (level[rows_] == s).all(), f"level {s} rows [{r0},{r1}) taken twice or out of order"
-        level[rows_] += 1
-    assert (level == k).all()                           # every row took every level exactly once
-    # working set of a band: (H + k) rows stay within ~70 MB unless the caller forced the band height
-    if rows == 0:
-        row_bytes = 9 * ny * (8 if prec == "dp" else 4)
-        tall = max(r1 - r0 for _, r0, r1 in launches)
-        assert (tall + k) * row_bytes <= 70e6 or tall <= 2 * k + 2
+    _check(nx, ny, k, launches)
+    if 0 < cols < ny and ny % 8 == 0 and 16 * k + 8 <= ny:
+        assert any(j1 > j0 for _, _, _, j0, j1 in launches), "column strips were asked for and possible"
+    # working set of a tile: (H + k) x (W + 8k) sites stay within ~70 MB unless the caller forced the sizes
+    if rows == 0 and cols == 0:
+        site = 9 * (8 if prec == "dp" else 4)
+        worst = max((r1 - r0 + k) * ((j1 - j0 + 8 * k) if j1 > j0 else ny) for _, r0, r1, j0, j1 in launches)
+        assert worst * site <= 70e6 or max(r1 - r0 for _, r0, r1, _, _ in launches) <= 2 * k + 2
+
+
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+def test_wide_lattices_get_column_strips_by_default(prec):
+    """8192x32768 (the weak-scaling unit): full-width bands would be ~19 rows, so the automatic plan cuts strips;
+    the area of all launches is k * nx * ny and no tile (with its skew margins) exceeds the L2 budget."""
+    nx, ny, k = 8192, 32768, 8
+    used, launches = tb_schedule(nx, ny, k, 0, 0, prec)
+    assert used == k and all(j1 > j0 for _, _, _, j0, j1 in launches)
+    area = sum((r1 - r0) * (j1 - j0) for _, r0, r1, j0, j1 in launches)
+    assert area == k * nx * ny
+    site = 9 * (8 if prec == "dp" else 4)
+    assert max((r1 - r0 + k) * (j1 - j0 + 8 * k) for _, r0, r1, j0, j1 in launches) * site <= 70e6
 
 
 def test_bad_arguments():
