@@ -89,6 +89,7 @@ struct lbm_ctx {
 	int graph_pairs;
 	cudaGraphExec_t wf_exec;     // captured wavefront macro-step (wf_k timesteps, bands of wf_h rows)
 	long long wf_launches;       // kernels in that graph
+	int in_wavefront;            // set while run_wavefront enqueues (step kernels may then use PDL on slabs too)
 };
 
 namespace {
@@ -245,6 +246,14 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	 * 43.7 vs 41.1 GLUPS at 400x4000 (profiles/r01_run3); no gain for SP or for large lattices */
 	c->tune.pdl = default_small_dp(c);
 	c->tune.graph = default_small_dp(c) ? 10 : 0;
+	if (c->inplace && (unsigned long long)c->nxl * c->ny > (16ull << 20)) {
+		/* wide / large in-place lattices (profiles/r01_run14): 2-D tiles of ~60 MB, plain PDL launches (replaying
+		 * thousands of kernel nodes from a graph measured 5-10 % slower).  DP 8192x32768: 62.1 vs 47.8 GLUPS. */
+		c->tune.pdl = 1;
+		c->tune.graph = 0;
+		c->tune.tb_depth = sizeof(real_t) == 8 ? 16 : 8;
+		c->tune.vec = sizeof(real_t) == 8 ? 1 : 4;
+	}
 	if (c->inplace && (unsigned long long)c->nxl * c->ny <= (16ull << 20)) {
 		/* in-place small lattices (profiles/r01_run8, r01_run9): PDL + graph replay for both precisions; lattices
 		 * beyond what the L2 keeps (~60 MB) whose rows are narrow enough for >= 64-row bands are swept with
@@ -368,7 +377,7 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			if (grid > cap) grid = cap;
 		}
 		/* PDL only where consecutive step kernels follow each other on one stream with nothing between */
-		const int pdl = c->tune.pdl && c->sync_mode == SYNC_SELF && c->nyvec == c->ny;
+		const int pdl = c->tune.pdl && (c->sync_mode == SYNC_SELF || c->in_wavefront) && c->nyvec == c->ny;
 		cudaError_t e;
 		if (c->inplace) {
 			const int phase = src == 0 ? 1 : 2;
@@ -588,18 +597,24 @@ void tb_axis(TbAxis *ax, int n, int g, int k, int P)
 
 /* depth, row bands and column strips actually used for a ring of nx rows x ny columns (k == 0: plain stepping).
  * tb_cols: 0 = automatic (strips only where full-width bands would be lower than 64 rows), >= ny = full width */
-void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int tb_depth, int tb_rows, int tb_cols)
+/* multi != 0: this slab is one of several.  Every slab of a ring must then walk the SAME sequence of (column piece,
+ * level) events, so the depth is never clamped to the slab: a slab too low for the row pyramid (2k + 2 > nx)
+ * takes whole-slab launches per event instead of row pieces. */
+void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols)
 {
 	const int G = 8;                                             /* column skew per level: keeps every vector width aligned */
 	int k = tb_depth & ~1;
-	while (k >= 2 && 2 * k + 2 > nx) k -= 2;                     /* pyramid base >= 2k inside the ring */
+	if (!multi)
+		while (k >= 2 && 2 * k + 2 > nx) k -= 2;                 /* pyramid base >= 2k inside the ring */
 	pl->k = k < 2 ? 0 : k;
 	if (!pl->k) return;
-	const double budget = sizeof(real_t) == 8 ? 45e6 : 60e6;     /* bytes of a tile incl. its skew margin: measured best, profiles/r01_run9,10 */
 	const double cell = 9.0 * sizeof(real_t);
+	/* bytes of a tile incl. its skew margins, measured best: bands 45 MB (DP) / 60 MB (SP) (profiles/r01_run9,10),
+	 * 2-D tiles 60 MB with 16 KB row segments (profiles/r01_run14) */
+	double budget = sizeof(real_t) == 8 ? 45e6 : 60e6;
 	int W = tb_cols;
 	if (!strips_ok || ny % G || 2 * G * k + G > ny) W = ny;      /* strips need aligned, wide enough rows */
-	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)(32768 / sizeof(real_t));   /* 32 KB row segments */
+	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)(16384 / sizeof(real_t));
 	if (W >= ny) {
 		pl->cols.n = ny; pl->cols.g = G; pl->cols.npieces = 1;
 		pl->cols.piece[0] = TbPiece{TB_WHOLE, 0, ny};
@@ -608,6 +623,12 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int tb_depth, i
 		W = (W + G - 1) / G * G;
 		tb_axis(&pl->cols, ny, G, k, W);
 		W += G * k;
+		budget = 60e6;
+	}
+	if (2 * k + 2 > nx) {                                        /* (multi only) no room for the row pyramid */
+		pl->rows.n = nx; pl->rows.g = 1; pl->rows.npieces = 1;
+		pl->rows.piece[0] = TbPiece{TB_WHOLE, 0, nx};
+		return;
 	}
 	int H = tb_rows;
 	if (H <= 0) H = (int)(budget / (cell * W)) - k;
@@ -617,6 +638,11 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int tb_depth, i
 /* the launches of one macro-step of kk <= pl.k levels, in order: visit(level, r0, r1, j0, j1); r1 / j1 may exceed
  * nx / ny (the range wraps); j0 == j1 == 0 means whole rows.  Column pieces outermost, row pieces next, levels
  * innermost: valid because each axis' piece order is (1-D argument in DESIGN.md) and the tile is their product. */
+/* `seam` tells a slab of a multi-slab ring where its two boundary rows (first and last row, whose neighbours live
+ * in other slabs) take the level within this column piece: bit 0 = the launch is the FIRST one of that (column
+ * piece, level) event to touch a boundary row -> wait for the neighbours' previous event before it; bit 1 = it is
+ * the LAST one -> announce the event after it.  Level 0: row 0 sits in the pyramid, the last row in the last
+ * parallelogram; levels >= 1: both sit in the inverted pyramid.  Whole-slab pieces are both at once. */
 template <typename F> int tb_for_each_launch(const TbPlan &pl, int kk, F visit)
 {
 	int rc;
@@ -624,19 +650,29 @@ template <typename F> int tb_for_each_launch(const TbPlan &pl, int kk, F visit)
 		for (int ri = 0; ri < pl.rows.npieces; ri++)
 			for (int s = 0; s < kk; s++) {
 				int r0, r1, j0, j1;
+				const int rt = pl.rows.piece[ri].type;
 				tb_range(pl.rows, pl.rows.piece[ri], s, &r0, &r1);
 				tb_range(pl.cols, pl.cols.piece[ci], s, &j0, &j1);
 				if (r1 <= r0 || j1 <= j0) continue;                  /* inverted pyramids are empty at level 0 */
 				if (pl.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
-				if ((rc = visit(s, r0, r1, j0, j1))) return rc;
+				int seam = 0;
+				if (rt == TB_WHOLE || rt == TB_INVERTED) seam = 3;
+				else if (rt == TB_PYRAMID && s == 0) seam = 1;
+				else if (rt == TB_PARALLELOGRAM && s == 0 && ri == pl.rows.npieces - 2) seam = 2;
+				if ((rc = visit(s, r0, r1, j0, j1, seam))) return rc;
 			}
 	return 0;
 }
 
 int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 {
-	return tb_for_each_launch(pl, kk, [&](int s, int r0, int r1, int j0, int j1) {
-		return launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1);
+	const bool flags = c->sync_mode == SYNC_FLAGS;
+	return tb_for_each_launch(pl, kk, [&](int s, int r0, int r1, int j0, int j1, int seam) {
+		int rc;
+		if (flags && (seam & 1) && (rc = launch_wait(c, c->stream[0]))) return rc;
+		if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1))) return rc;
+		if (flags && (seam & 2) && (rc = launch_signal(c, c->stream[0]))) return rc;
+		return (int)LBM_OK;
 	});
 }
 
@@ -644,7 +680,8 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 {
 	int rc;
 	static thread_local TbPlan pl;                               /* ~25 KB: not on the stack of every call */
-	tb_plan(&pl, c->nxl, c->ny, c->ldy, c->inplace && c->vw > 1 && c->nyvec == c->ny, c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
+	tb_plan(&pl, c->nxl, c->ny, c->ldy, c->inplace && c->vw > 1 && c->nyvec == c->ny, c->sync_mode == SYNC_FLAGS,
+	        c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
 	const int k = pl.k;
 	if (k < 2) {
 		for (int t = 0; t < nsteps; t++)
@@ -652,7 +689,8 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 		return LBM_OK;
 	}
 	int t = 0;
-	if (c->tune.graph > 0 && nsteps - k >= k) {
+	struct Scope { lbm_ctx *c; Scope(lbm_ctx *c_) : c(c_) { c->in_wavefront = 1; } ~Scope() { c->in_wavefront = 0; } } scope(c);
+	if (c->tune.graph > 0 && nsteps - k >= k && c->sync_mode == SYNC_SELF) {      /* slabs: the epochs of wait/signal change per launch */
 		if (!c->wf_exec) {                                       /* any change of tuning drops the graph */
 			cudaGraph_t g = nullptr;
 			CK(cudaStreamBeginCapture(c->stream[0], cudaStreamCaptureModeThreadLocal));
@@ -856,7 +894,7 @@ int lbm_run(lbm_ctx *c, int nsteps)
 	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
 	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
 	if (use_persistent(c)) return launch_persistent(c, LBM_BUF_A, nsteps, 0, c->stream[0]);
-	if (c->inplace && c->sync_mode == SYNC_SELF && c->tune.tb_depth >= 2) return run_wavefront(c, nsteps);
+	if (c->inplace && (c->sync_mode == SYNC_SELF || c->sync_mode == SYNC_FLAGS) && c->tune.tb_depth >= 2) return run_wavefront(c, nsteps);
 	int t = 0;
 	if (c->tune.graph > 0 && c->sync_mode == SYNC_SELF) {
 		/* replay whole (A->B, B->A) pairs, all with the tail source, from a captured graph; the last
@@ -1073,11 +1111,11 @@ int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int tb_cols, int 
 	const int per128 = 128 / (int)sizeof(real_t);
 	const int ldy = ((ny + per128 - 1) / per128) * per128;
 	static thread_local TbPlan pl;
-	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, tb_depth, tb_rows, tb_cols);
+	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, 0, tb_depth, tb_rows, tb_cols);
 	if (depth_used) *depth_used = pl.k;
 	if (pl.k < 2) return 0;
 	int n = 0;
-	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1) {
+	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1, int) {
 		if (n < cap) { int *o = launches + 5 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; }
 		n++;
 		return 0;

@@ -24,17 +24,25 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     ok = True
-    for prec, transport, nx, ny, inplace in (("dp", "p2p", 803, 2000, False), ("sp", "p2p", 803, 2000, False), ("dp", "staged", 401, 1000, False),
-                                             ("dp", "p2p", world, 64, False), ("sp", "p2p", 2 * world + 1, 264, False),
-                                             # one buffer per slab, in-place kernels: phase-1 boundary rows store into the neighbour's OWNED rows
-                                             ("dp", "p2p", 803, 2000, True), ("sp", "p2p", 803, 2000, True),
-                                             ("dp", "p2p", world, 64, True), ("sp", "p2p", 2 * world + 1, 264, True)):
+    CASES = [("dp", "p2p", 803, 2000, False), ("sp", "p2p", 803, 2000, False), ("dp", "staged", 401, 1000, False),
+             ("dp", "p2p", world, 64, False), ("sp", "p2p", 2 * world + 1, 264, False),
+             # one buffer per slab, in-place kernels: phase-1 boundary rows store into the neighbour's OWNED rows
+             ("dp", "p2p", 803, 2000, True), ("sp", "p2p", 803, 2000, True),
+             ("dp", "p2p", world, 64, True), ("sp", "p2p", 2 * world + 1, 264, True),
+             # + temporal blocking across the slab seams: (depth, band rows, strip columns); slabs too low for the
+             # row pyramid take whole-slab launches per event
+             ("dp", "p2p", 803, 2000, dict(tb_depth=4, tb_rows=50, tb_cols=0)), ("sp", "p2p", 803, 2000, dict(tb_depth=6, tb_rows=0, tb_cols=256)),
+             ("dp", "p2p", 803, 2000, dict(tb_depth=16, tb_rows=33, tb_cols=512, vec=1)), ("dp", "p2p", world, 64, dict(tb_depth=2, tb_rows=0, tb_cols=0)),
+             ("sp", "p2p", 2 * world + 1, 264, dict(tb_depth=4, tb_rows=0, tb_cols=64)), ("dp", "p2p", 7 * world + 3, 520, dict(tb_depth=4, tb_rows=2, tb_cols=104))]
+    for prec, transport, nx, ny, inplace in CASES:
         c = dict(prec=prec, isa="avx", nx=nx, ny=ny, scene="cylinder" if nx > 100 else "random", perturb=None if nx > 100 else 3)
         fA, walls = cases.make_inputs(c)
         if nx <= 100:                              # tiny lattices: no channel rows (they would leave no fluid row)
             walls[:] = 0
             walls[0, ::5] = 1
-        dl = DistributedLattice(nx, ny, prec, transport, device=local, inplace=inplace)
+        dl = DistributedLattice(nx, ny, prec, transport, device=local, inplace=bool(inplace))
+        if isinstance(inplace, dict):
+            dl.lat.set_tuning(**inplace)
         dl.lat.upload(fA, walls)
         dist.barrier()
         t0 = time.time()
@@ -57,7 +65,7 @@ def main():
             if not inplace:
                 same = same and np.concatenate(parts_b, axis=1).tobytes() == want_b.tobytes()
             ok &= same
-            print(f"[mgpu] {prec} {transport}{' in-place' if inplace else ''} {nx}x{ny} over {world} GPUs: {'BIT-EXACT' if same else 'MISMATCH'} vs single GPU (A/B) "
+            print(f"[mgpu] {prec} {transport}{' in-place' if inplace else ''}{' ' + str(inplace) if isinstance(inplace, dict) else ''} {nx}x{ny} over {world} GPUs: {'BIT-EXACT' if same else 'MISMATCH'} vs single GPU (A/B) "
                   f"(Re {re!r} vs {want_re!r}; {dt:.2f} s)", flush=True)
             if not same:
                 bad = np.argwhere(got != want)
