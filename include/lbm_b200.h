@@ -197,12 +197,14 @@ int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
 /* Kernels launched by this context since creation (bench.py's gpu_launches). */
 long long lbm_kernel_launches(lbm_ctx *ctx);
-/* The launch list of ONE temporal-blocking macro-step for a single-slab ring of nx rows x ny columns (host logic
- * only, no GPU needed): launches[5n..5n+4] = (level, r0, r1, j0, j1): rows [r0,r1) and columns [j0,j1), either
- * range may run past nx / ny and then wraps periodically; j0 == j1 == 0 means whole rows.  *depth_used = the depth
- * after clamping to the ring (0: the lattice is too small, plain stepping is used).  Returns the number of
- * launches (which may exceed cap; only cap entries are written), -1 on bad arguments. */
-int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
+/* The launch list of ONE temporal-blocking macro-step for a slab of nx rows x ny columns (host logic only, no GPU
+ * needed): launches[6n..6n+5] = (level, r0, r1, j0, j1, seam): rows [r0,r1) and columns [j0,j1), either range may
+ * run past nx / ny and then wraps (rows: into the ring neighbours when multi != 0); j0 == j1 == 0 means whole rows.
+ * seam (slabs of a multi-slab ring, multi != 0): bit 0 = wait for both neighbours' previous event before this
+ * launch, bit 1 = announce this slab's event after it.  *depth_used = the depth used (single slab: clamped to the
+ * ring, 0 = lattice too small, plain stepping).  Returns the number of launches (which may exceed cap; only cap
+ * entries are written), -1 on bad arguments. */
+int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
 
 #ifdef __cplusplus
 }

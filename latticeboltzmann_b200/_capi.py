@@ -88,7 +88,7 @@ class Lib:
         d.lbm_kernel_launches.argtypes = [vp]
         d.lbm_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(self.Config)]
         d.lbm_tb_schedule.restype = ci
-        d.lbm_tb_schedule.argtypes = [ci, ci, ci, ci, ci, ctypes.POINTER(ci), vp, ci]
+        d.lbm_tb_schedule.argtypes = [ci, ci, ci, ci, ci, ci, ctypes.POINTER(ci), vp, ci]
         for name, args in {
             "lbm_destroy": [vp], "lbm_initialize_arrays": [vp, ctypes.POINTER(self.Scene)],
             "lbm_upload": [vp, vp, vp, vp, ci], "lbm_download": [vp, vp, vp, vp, ci],

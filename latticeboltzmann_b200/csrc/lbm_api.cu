@@ -614,7 +614,8 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int 
 	double budget = sizeof(real_t) == 8 ? 45e6 : 60e6;
 	int W = tb_cols;
 	if (!strips_ok || ny % G || 2 * G * k + G > ny) W = ny;      /* strips need aligned, wide enough rows */
-	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)(16384 / sizeof(real_t));
+	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)((multi ? 32768 : 16384) / sizeof(real_t));   /* slabs: fewer, wider
+	                                                                  strips -- every (strip, level) costs a handshake with both neighbours */
 	if (W >= ny) {
 		pl->cols.n = ny; pl->cols.g = G; pl->cols.npieces = 1;
 		pl->cols.piece[0] = TbPiece{TB_WHOLE, 0, ny};
@@ -1105,18 +1106,18 @@ int lbm_get_tuning(lbm_ctx *c, lbm_tuning *t)
 }
 long long lbm_kernel_launches(lbm_ctx *c) { return c ? c->launches : 0; }
 
-int lbm_tb_schedule(int nx, int ny, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap)
+int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap)
 {
 	if (nx < 1 || ny < 2 || tb_depth < 0 || tb_rows < 0 || tb_cols < 0 || (cap > 0 && !launches)) { fail(LBM_ERR_ARG, "lbm_tb_schedule: bad argument"); return -1; }
 	const int per128 = 128 / (int)sizeof(real_t);
 	const int ldy = ((ny + per128 - 1) / per128) * per128;
 	static thread_local TbPlan pl;
-	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, 0, tb_depth, tb_rows, tb_cols);
+	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi != 0, tb_depth, tb_rows, tb_cols);
 	if (depth_used) *depth_used = pl.k;
 	if (pl.k < 2) return 0;
 	int n = 0;
-	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1, int) {
-		if (n < cap) { int *o = launches + 5 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; }
+	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1, int seam) {
+		if (n < cap) { int *o = launches + 6 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; o[5] = seam; }
 		n++;
 		return 0;
 	});

@@ -74,3 +74,59 @@ def test_bad_arguments():
     from latticeboltzmann_b200 import LbmError
     with pytest.raises(LbmError):
         tb_schedule(0, 64, 4)
+
+
+# ---------------------------------------------------------------------------------------------------
+# several slabs: every slab walks its own launch list; the only coupling is the event protocol of
+# lbm_tb_schedule's `seam` bits (wait: both ring neighbours have announced as many events as I have;
+# announce: after the launch).  Any interleaving the protocol allows must respect the global dependencies.
+# ---------------------------------------------------------------------------------------------------
+RINGS = [  # (slab heights, ny, depth, rows, cols)
+    ([40, 40], 264, 4, 9, 64), ([41, 40, 40], 136, 6, 0, 0), ([30, 5, 30], 264, 8, 7, 64),      # middle slab too low: whole-slab launches
+    ([3, 3, 3, 3], 64, 2, 0, 0), ([1, 1], 64, 2, 0, 0), ([50, 49], 520, 16, 12, 104), ([20, 21, 20, 21, 20], 40, 4, 5, 0),
+]
+
+
+@pytest.mark.parametrize("heights,ny,depth,rows,cols", RINGS)
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_slab_ring_event_protocol(heights, ny, depth, rows, cols, seed):
+    P, nx = len(heights), sum(heights)
+    lo = np.concatenate([[0], np.cumsum(heights)[:-1]])
+    lists = []
+    for h in heights:
+        k, launches = tb_schedule(h, ny, depth, rows, cols, "dp", multi=True)
+        assert k == depth                               # never clamped per slab: all slabs walk the same events
+        lists.append(launches)
+    n_events = [sum(1 for l in ls if l[5] & 2) for ls in lists]
+    assert len(set(n_events)) == 1, f"slabs disagree on the number of events: {n_events}"
+    level = np.zeros((nx, ny), dtype=np.int16)
+    pos, announced = [0] * P, [0] * P
+    rng = np.random.default_rng(seed)
+    while any(pos[p] < len(lists[p]) for p in range(P)):
+        runnable = []
+        for p in range(P):
+            if pos[p] == len(lists[p]):
+                continue
+            seam = lists[p][pos[p]][5]
+            if (seam & 1) and (announced[(p + 1) % P] < announced[p] or announced[(p - 1) % P] < announced[p]):
+                continue
+            runnable.append(p)
+        assert runnable, f"deadlock at positions {pos}, announced {announced}"
+        p = int(rng.choice(runnable))
+        s, r0, r1, j0, j1, seam = lists[p][pos[p]]
+        if j0 == j1 == 0:
+            j1 = ny
+        h = heights[p]
+        rws = lo[p] + (np.arange(r0, r1) % h)           # rows past the slab wrap INSIDE the slab (its first rows)
+        cls = np.arange(j0, j1) % ny
+        assert len(set(rws.tolist())) == len(rws)
+        assert (level[np.ix_(rws, cls)] == s).all(), f"slab {p} level {s} rows [{r0},{r1}) cols [{j0},{j1}) out of order"
+        for di in (-1, 0, 1):
+            for dj in (-1, 0, 1):
+                assert (level[np.ix_((rws + di) % nx, (cls + dj) % ny)] >= s).all(), \
+                    f"slab {p} level {s} rows [{r0},{r1}) cols [{j0},{j1}): neighbour ({di:+d},{dj:+d}) behind (seam {seam})"
+        level[np.ix_(rws, cls)] = s + 1
+        if seam & 2:
+            announced[p] += 1
+        pos[p] += 1
+    assert (level == depth).all()
