@@ -564,7 +564,7 @@ int enqueue_step(lbm_ctx *c, int src, int tail_source)
 // g = cells the piece boundaries move per level (>= the stencil reach 1; 8 along j keeps vectors aligned).
 struct TbPiece { int type, a, b; };
 enum { TB_PYRAMID = 0, TB_PARALLELOGRAM = 1, TB_INVERTED = 2, TB_WHOLE = 3 };
-struct TbAxis { int n, g, npieces; TbPiece piece[1026]; };
+struct TbAxis { int n, g, e, npieces; TbPiece piece[1026]; };   /* e: cells at either end of the axis kept for the inverted pyramid at level 0 */
 struct TbPlan { int k; TbAxis rows, cols; };
 
 inline void tb_range(const TbAxis &ax, const TbPiece &pc, int s, int *lo, int *hi)
@@ -572,25 +572,28 @@ inline void tb_range(const TbAxis &ax, const TbPiece &pc, int s, int *lo, int *h
 	switch (pc.type) {
 	case TB_PYRAMID: *lo = pc.a + ax.g * s; *hi = pc.b - ax.g * s; break;
 	case TB_PARALLELOGRAM: *lo = pc.a - ax.g * s; *hi = pc.b - ax.g * s; break;
-	case TB_INVERTED: *lo = ax.n - ax.g * s; *hi = ax.n + ax.g * s; break;
+	case TB_INVERTED: *lo = ax.n - ax.e - ax.g * s; *hi = ax.n + ax.e + ax.g * s; break;
 	default: *lo = 0; *hi = ax.n; break;
 	}
 }
 
-/* pieces of one axis: pyramid base P0 >= 2 g k, then equal parallelograms of ~P cells, then the inverted pyramid */
-void tb_axis(TbAxis *ax, int n, int g, int k, int P)
+/* pieces of one axis: pyramid [e, P0) with P0 - e >= 2 g k, then equal parallelograms of ~P cells up to n - e, then
+ * the inverted pyramid.  e = 1 on the row axis of a slab: its first and last row (whose neighbours live in other
+ * slabs) then belong to the inverted pyramid at EVERY level, so that piece alone talks to the neighbours. */
+void tb_axis(TbAxis *ax, int n, int g, int e, int k, int P)
 {
-	ax->n = n; ax->g = g; ax->npieces = 0;
+	ax->n = n; ax->g = g; ax->e = e; ax->npieces = 0;
 	if (P < 2 * g) P = 2 * g;
-	int P0 = P < 2 * g * k ? 2 * g * k : P;
-	if (P0 > n - g) P0 = n - g;
+	int P0 = P < 2 * g * k + e ? 2 * g * k + e : P;
+	if (P0 > n - e - g) P0 = n - e - g;
 	P0 = P0 / g * g;
-	ax->piece[ax->npieces++] = TbPiece{TB_PYRAMID, 0, P0};
-	if (n - P0 > 0) {
-		int nb = (n - P0 + P - 1) / P;
+	ax->piece[ax->npieces++] = TbPiece{TB_PYRAMID, e, P0};
+	const int end = n - e;
+	if (end - P0 > 0) {
+		int nb = (end - P0 + P - 1) / P;
 		if (nb > 1023) nb = 1023;
-		int Pe = ((n - P0 + nb - 1) / nb + g - 1) / g * g;       /* equal pieces instead of a short last one */
-		for (int a = P0; a < n; a += Pe) ax->piece[ax->npieces++] = TbPiece{TB_PARALLELOGRAM, a, a + Pe < n ? a + Pe : n};
+		int Pe = ((end - P0 + nb - 1) / nb + g - 1) / g * g;     /* equal pieces instead of a short last one */
+		for (int a = P0; a < end; a += Pe) ax->piece[ax->npieces++] = TbPiece{TB_PARALLELOGRAM, a, a + Pe < end ? a + Pe : end};
 	}
 	ax->piece[ax->npieces++] = TbPiece{TB_INVERTED, 0, 0};
 }
@@ -617,33 +620,32 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int 
 	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)((multi ? 32768 : 16384) / sizeof(real_t));   /* slabs: fewer, wider
 	                                                                  strips -- every (strip, level) costs a handshake with both neighbours */
 	if (W >= ny) {
-		pl->cols.n = ny; pl->cols.g = G; pl->cols.npieces = 1;
+		pl->cols.n = ny; pl->cols.g = G; pl->cols.e = 0; pl->cols.npieces = 1;
 		pl->cols.piece[0] = TbPiece{TB_WHOLE, 0, ny};
 		W = ldy;
 	} else {
 		W = (W + G - 1) / G * G;
-		tb_axis(&pl->cols, ny, G, k, W);
+		tb_axis(&pl->cols, ny, G, 0, k, W);
 		W += G * k;
 		budget = 60e6;
 	}
-	if (2 * k + 2 > nx) {                                        /* (multi only) no room for the row pyramid */
-		pl->rows.n = nx; pl->rows.g = 1; pl->rows.npieces = 1;
+	if (2 * k + 2 + 2 * (multi != 0) > nx) {                     /* (multi only) no room for the row pyramid */
+		pl->rows.n = nx; pl->rows.g = 1; pl->rows.e = 0; pl->rows.npieces = 1;
 		pl->rows.piece[0] = TbPiece{TB_WHOLE, 0, nx};
 		return;
 	}
 	int H = tb_rows;
 	if (H <= 0) H = (int)(budget / (cell * W)) - k;
-	tb_axis(&pl->rows, nx, 1, k, H < 2 ? 2 : H);
+	tb_axis(&pl->rows, nx, 1, multi != 0, k, H < 2 ? 2 : H);
 }
 
 /* the launches of one macro-step of kk <= pl.k levels, in order: visit(level, r0, r1, j0, j1); r1 / j1 may exceed
  * nx / ny (the range wraps); j0 == j1 == 0 means whole rows.  Column pieces outermost, row pieces next, levels
  * innermost: valid because each axis' piece order is (1-D argument in DESIGN.md) and the tile is their product. */
-/* `seam` tells a slab of a multi-slab ring where its two boundary rows (first and last row, whose neighbours live
- * in other slabs) take the level within this column piece: bit 0 = the launch is the FIRST one of that (column
- * piece, level) event to touch a boundary row -> wait for the neighbours' previous event before it; bit 1 = it is
- * the LAST one -> announce the event after it.  Level 0: row 0 sits in the pyramid, the last row in the last
- * parallelogram; levels >= 1: both sit in the inverted pyramid.  Whole-slab pieces are both at once. */
+/* `seam` (slabs of a multi-slab ring): 3 = this launch contains the slab's first and last row, whose neighbours
+ * live in other slabs -- wait for both neighbours' previous event before it (bit 0) and announce this slab's event
+ * after it (bit 1); 0 = the launch depends on this slab's own rows only.  With e = 1 on the row axis those are
+ * exactly the inverted-pyramid launches (one per column piece and level); whole-slab pieces likewise. */
 template <typename F> int tb_for_each_launch(const TbPlan &pl, int kk, F visit)
 {
 	int rc;
@@ -656,25 +658,44 @@ template <typename F> int tb_for_each_launch(const TbPlan &pl, int kk, F visit)
 				tb_range(pl.cols, pl.cols.piece[ci], s, &j0, &j1);
 				if (r1 <= r0 || j1 <= j0) continue;                  /* inverted pyramids are empty at level 0 */
 				if (pl.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
-				int seam = 0;
-				if (rt == TB_WHOLE || rt == TB_INVERTED) seam = 3;
-				else if (rt == TB_PYRAMID && s == 0) seam = 1;
-				else if (rt == TB_PARALLELOGRAM && s == 0 && ri == pl.rows.npieces - 2) seam = 2;
+				const int seam = (rt == TB_WHOLE || rt == TB_INVERTED) ? 3 : 0;
 				if ((rc = visit(s, r0, r1, j0, j1, seam))) return rc;
 			}
 	return 0;
 }
 
+/* Single slab: everything on stream 0.  Slab of a ring: the seam launches (inverted row pyramid: the only ones that
+ * read or write another slab) form a chain on stream 1 -- wait for the neighbours' previous event, launch, announce --
+ * that starts once this column piece's own tiles are done and runs beside the NEXT column piece's tiles on stream 0
+ * (those never depend on seam rows of the same macro-step); the streams join at the end of the macro-step. */
 int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 {
 	const bool flags = c->sync_mode == SYNC_FLAGS;
-	return tb_for_each_launch(pl, kk, [&](int s, int r0, int r1, int j0, int j1, int seam) {
-		int rc;
-		if (flags && (seam & 1) && (rc = launch_wait(c, c->stream[0]))) return rc;
-		if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1))) return rc;
-		if (flags && (seam & 2) && (rc = launch_signal(c, c->stream[0]))) return rc;
-		return (int)LBM_OK;
+	bool chain_open = false;
+	cudaError_t ce = cudaSuccess;
+	int rc = tb_for_each_launch(pl, kk, [&](int s, int r0, int r1, int j0, int j1, int seam) {
+		int r;
+		const int tail = t0 + s != nsteps - 1;
+		if (!(flags && seam)) {
+			chain_open = false;
+			return launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[0], j0, j1);
+		}
+		if (!chain_open) {
+			if ((ce = cudaEventRecord(c->ev_main, c->stream[0])) != cudaSuccess) return (int)LBM_ERR_CUDA;
+			if ((ce = cudaStreamWaitEvent(c->stream[1], c->ev_main, 0)) != cudaSuccess) return (int)LBM_ERR_CUDA;
+			chain_open = true;
+		}
+		if ((r = launch_wait(c, c->stream[1]))) return r;
+		if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[1], j0, j1))) return r;
+		return launch_signal(c, c->stream[1]);
 	});
+	if (ce != cudaSuccess) return fail(LBM_ERR_CUDA, "enqueue_macro: %s", cudaGetErrorString(ce));
+	if (rc) return rc;
+	if (flags) {
+		CK(cudaEventRecord(c->ev_bnd[0], c->stream[1]));
+		CK(cudaStreamWaitEvent(c->stream[0], c->ev_bnd[0], 0));
+	}
+	return LBM_OK;
 }
 
 int run_wavefront(lbm_ctx *c, int nsteps)

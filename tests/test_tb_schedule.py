@@ -90,30 +90,26 @@ RINGS = [  # (slab heights, ny, depth, rows, cols)
 @pytest.mark.parametrize("heights,ny,depth,rows,cols", RINGS)
 @pytest.mark.parametrize("seed", [0, 1, 2])
 def test_slab_ring_event_protocol(heights, ny, depth, rows, cols, seed):
+    """Two in-order queues per slab, as enqueue_macro builds them: stream 0 takes the launches without seam bits,
+    stream 1 the seam chain; a chain launch starts only after every stream-0 launch listed before it (the event
+    recorded when the chain of a column piece opens) and after both neighbours have announced as many events as
+    this slab has.  Any interleaving allowed by that must respect the global 3x3 dependencies."""
     P, nx = len(heights), sum(heights)
     lo = np.concatenate([[0], np.cumsum(heights)[:-1]])
-    lists = []
+    main, chain = [], []
     for h in heights:
         k, launches = tb_schedule(h, ny, depth, rows, cols, "dp", multi=True)
         assert k == depth                               # never clamped per slab: all slabs walk the same events
-        lists.append(launches)
-    n_events = [sum(1 for l in ls if l[5] & 2) for ls in lists]
-    assert len(set(n_events)) == 1, f"slabs disagree on the number of events: {n_events}"
+        assert all(l[5] in (0, 3) for l in launches)
+        main.append([(i, l) for i, l in enumerate(launches) if l[5] == 0])
+        chain.append([(i, l) for i, l in enumerate(launches) if l[5] == 3])
+    assert len({len(c) for c in chain}) == 1, "slabs disagree on the number of events"
     level = np.zeros((nx, ny), dtype=np.int16)
-    pos, announced = [0] * P, [0] * P
+    mpos, cpos = [0] * P, [0] * P
     rng = np.random.default_rng(seed)
-    while any(pos[p] < len(lists[p]) for p in range(P)):
-        runnable = []
-        for p in range(P):
-            if pos[p] == len(lists[p]):
-                continue
-            seam = lists[p][pos[p]][5]
-            if (seam & 1) and (announced[(p + 1) % P] < announced[p] or announced[(p - 1) % P] < announced[p]):
-                continue
-            runnable.append(p)
-        assert runnable, f"deadlock at positions {pos}, announced {announced}"
-        p = int(rng.choice(runnable))
-        s, r0, r1, j0, j1, seam = lists[p][pos[p]]
+
+    def run(p, launch):
+        s, r0, r1, j0, j1, seam = launch
         if j0 == j1 == 0:
             j1 = ny
         h = heights[p]
@@ -125,8 +121,26 @@ def test_slab_ring_event_protocol(heights, ny, depth, rows, cols, seed):
             for dj in (-1, 0, 1):
                 assert (level[np.ix_((rws + di) % nx, (cls + dj) % ny)] >= s).all(), \
                     f"slab {p} level {s} rows [{r0},{r1}) cols [{j0},{j1}): neighbour ({di:+d},{dj:+d}) behind (seam {seam})"
+        if not seam and P > 1:                          # stream-0 launches must not touch another slab's rows at all
+            assert ((rws - 1 >= lo[p]) & (rws + 1 < lo[p] + h)).all()
         level[np.ix_(rws, cls)] = s + 1
-        if seam & 2:
-            announced[p] += 1
-        pos[p] += 1
+
+    while any(mpos[p] < len(main[p]) or cpos[p] < len(chain[p]) for p in range(P)):
+        runnable = []
+        for p in range(P):
+            if mpos[p] < len(main[p]):
+                runnable.append((p, 0))
+            if cpos[p] < len(chain[p]):
+                idx = chain[p][cpos[p]][0]
+                main_done = mpos[p] == len(main[p]) or main[p][mpos[p]][0] > idx
+                if main_done and cpos[(p + 1) % P] >= cpos[p] and cpos[(p - 1) % P] >= cpos[p]:
+                    runnable.append((p, 1))
+        assert runnable, f"deadlock: main {mpos}, chain {cpos}"
+        p, q = runnable[int(rng.integers(len(runnable)))]
+        if q == 0:
+            run(p, main[p][mpos[p]][1])
+            mpos[p] += 1
+        else:
+            run(p, chain[p][cpos[p]][1])
+            cpos[p] += 1
     assert (level == depth).all()
