@@ -1239,6 +1239,78 @@ int lbm_connect_local(lbm_ctx *c, lbm_ctx *up, lbm_ctx *dn)
 	return LBM_OK;
 }
 
+/* lbm_group_run for in-place slabs with temporal blocking.  Every slab walks its own launch list (tb_plan, multi):
+ * tiles that touch only the slab's own rows on stream 0, the seam chain (inverted row pyramid, or whole-slab
+ * launches where the slab is too low) on stream 1.  Chain event (column piece, level) of a slab waits for the
+ * previous chain event of both neighbours; events are recorded only after every slab has enqueued its waits on
+ * the previous ones (two event objects per slab, alternating), as in the plain loop below. */
+static int group_run_wavefront(lbm_ctx **slabs, int n, int nsteps)
+{
+	int rc;
+	std::vector<TbPlan> plans((size_t)n);
+	for (int p = 0; p < n; p++) {
+		lbm_ctx *c = slabs[p];
+		tb_plan(&plans[p], c->nxl, c->ny, c->ldy, c->vw > 1 && c->nyvec == c->ny, 1, c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
+		c->in_wavefront = 1;
+	}
+	struct Done { lbm_ctx **s; int n; ~Done() { for (int p = 0; p < n; p++) s[p]->in_wavefront = 0; } } done{slabs, n};
+	const int k = plans[0].k;
+	const TbAxis &cols = plans[0].cols;                          /* identical on every slab (same ny, depth, tb_cols) */
+	int ev = 0;                                                  /* chain events so far: ev_bnd[ev & 1] is recorded next */
+	for (int t0 = 0; t0 < nsteps; t0 += k) {
+		const int kk = nsteps - t0 < k ? nsteps - t0 : k;
+		for (int ci = 0; ci < cols.npieces; ci++) {
+			for (int p = 0; p < n; p++) {                        /* own tiles of this column piece, all levels */
+				lbm_ctx *c = slabs[p];
+				const TbAxis &rows = plans[p].rows;
+				if ((rc = set_device(c))) return rc;
+				for (int ri = 0; ri < rows.npieces; ri++) {
+					if (rows.piece[ri].type == TB_INVERTED || rows.piece[ri].type == TB_WHOLE) continue;
+					for (int s = 0; s < kk; s++) {
+						int r0, r1, j0, j1;
+						tb_range(rows, rows.piece[ri], s, &r0, &r1);
+						tb_range(cols, cols.piece[ci], s, &j0, &j1);
+						if (r1 <= r0 || j1 <= j0) continue;
+						if (cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
+						if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1))) return rc;
+					}
+				}
+				CK(cudaEventRecord(c->ev_main, c->stream[0]));
+				CK(cudaStreamWaitEvent(c->stream[1], c->ev_main, 0));
+			}
+			for (int s = 0; s < kk; s++) {                       /* the seam chain, level by level, all slabs */
+				int j0, j1;
+				tb_range(cols, cols.piece[ci], s, &j0, &j1);
+				if (j1 <= j0) continue;
+				if (cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
+				const int cur = ev & 1, prev = cur ^ 1;
+				for (int p = 0; p < n; p++) {
+					lbm_ctx *c = slabs[p], *up = slabs[(p + 1) % n], *dn = slabs[(p + n - 1) % n];
+					const TbAxis &rows = plans[p].rows;
+					int r0, r1;
+					tb_range(rows, rows.piece[rows.npieces - 1], s, &r0, &r1);   /* inverted pyramid or the whole slab */
+					if ((rc = set_device(c))) return rc;
+					CK(cudaStreamWaitEvent(c->stream[1], up->ev_bnd[prev], 0));
+					CK(cudaStreamWaitEvent(c->stream[1], dn->ev_bnd[prev], 0));
+					if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[1], j0, j1))) return rc;
+				}
+				for (int p = 0; p < n; p++) {
+					lbm_ctx *c = slabs[p];
+					if ((rc = set_device(c))) return rc;
+					CK(cudaEventRecord(c->ev_bnd[cur], c->stream[1]));
+				}
+				ev++;
+			}
+		}
+		for (int p = 0; p < n; p++) {                            /* the next macro-step's tiles need the chains */
+			lbm_ctx *c = slabs[p];
+			if ((rc = set_device(c))) return rc;
+			CK(cudaStreamWaitEvent(c->stream[0], c->ev_bnd[(ev - 1) & 1], 0));
+		}
+	}
+	return LBM_OK;
+}
+
 /* All slabs of a ring that live in this process step together.  Per step and slab:
  * boundary rows on stream 1 once the neighbours' previous boundary kernels are done
  * (cross-device event waits), inner rows on stream 0 meanwhile, then join. */
@@ -1262,6 +1334,13 @@ int lbm_group_run(lbm_ctx **slabs, int n, int nsteps)
 		if ((rc = launch_halo_push(c, LBM_BUF_A, c->stream[0]))) return rc;
 		CK(cudaEventRecord(c->ev_bnd[1], c->stream[0]));
 	}
+	/* in-place slabs that all ask for the same temporal blocking: the slab schedule of run_wavefront, with events
+	 * between the seam chains instead of device flags */
+	bool tb = slabs[0]->inplace && slabs[0]->tune.tb_depth >= 2;
+	for (int k = 0; k < n && tb; k++)
+		tb = slabs[k]->inplace && slabs[k]->tune.tb_depth == slabs[0]->tune.tb_depth && slabs[k]->tune.tb_cols == slabs[0]->tune.tb_cols &&
+		     slabs[k]->ny == slabs[0]->ny && slabs[k]->nyvec == slabs[0]->nyvec && slabs[k]->vw == slabs[0]->vw;
+	if (tb) return group_run_wavefront(slabs, n, nsteps);
 	for (int t = 0; t < nsteps; t++) {
 		const int src = t & 1, tail = t != nsteps - 1, cur = t & 1, prev = cur ^ 1;
 		for (int k = 0; k < n; k++) {

@@ -263,7 +263,8 @@ def test_error_behaviour():
 # ---------------------------------------------------------------------------------------------
 # decomposition invariance: N logical slabs on one GPU == one slab, bit for bit
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("inplace", [False, True], ids=["ab", "inplace"])
+@pytest.mark.parametrize("inplace", [False, True, dict(tb_depth=4, tb_rows=7, tb_cols=128), dict(tb_depth=8, tb_rows=0, tb_cols=0, pdl=1)],
+                         ids=["ab", "inplace", "inplace+tb2d", "inplace+tb"])
 @pytest.mark.parametrize("prec,nslabs", [("dp", 2), ("dp", 3), ("dp", 8), ("sp", 4)])
 def test_slab_ring_equals_single_slab(prec, nslabs, inplace):
     from latticeboltzmann_b200 import Lattice, group_run, make_ring
@@ -273,9 +274,11 @@ def test_slab_ring_equals_single_slab(prec, nslabs, inplace):
         one.upload(fA, walls)
         one.run(c["steps"])
         want_a, want_b, want_re = one.download("A"), one.download("B"), one.ComputeReynolds()
-    ring = make_ring(c["nx"], c["ny"], nslabs, prec, inplace=inplace)
+    ring = make_ring(c["nx"], c["ny"], nslabs, prec, inplace=bool(inplace))
     try:
         for s in ring:
+            if isinstance(inplace, dict):
+                s.set_tuning(**inplace)                   # temporal blocking across the seams of lbm_group_run
             s.upload(fA, walls)
         group_run(ring, 20)
         group_run(ring, 40)
@@ -301,10 +304,12 @@ def test_uneven_slabs_and_single_row_slabs():
     fA, walls = cases.make_inputs(c)
     o = _oracle(c, fA, walls, c["steps"])
     for bounds, inplace in [(b, ip) for b in ([(0, 1), (1, 2), (2, 11)], [(0, 5), (5, 6), (6, 11)], [(k, k + 1) for k in range(11)])
-                            for ip in (False, True)]:
-        ring = make_ring(c["nx"], c["ny"], len(bounds), "dp", bounds=bounds, inplace=inplace)
+                            for ip in (False, True, dict(tb_depth=2, tb_rows=2, tb_cols=16), dict(tb_depth=4, tb_rows=0, tb_cols=0))]:
+        ring = make_ring(c["nx"], c["ny"], len(bounds), "dp", bounds=bounds, inplace=bool(inplace))
         try:
             for s in ring:
+                if isinstance(inplace, dict):
+                    s.set_tuning(**inplace)               # slabs too low for the row pyramid: whole-slab launches per event
                 s.upload(fA, walls)
             group_run(ring, c["steps"])
             got = np.zeros_like(fA)
