@@ -324,9 +324,11 @@ cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned
 template <int V>
 cudaError_t launch_aa_v(int phase, int pipe, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
 {
-	if (pipe)
+	if (pipe == 1)
 		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 1>, p, grid, block, st, pdl)
 		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 1>, p, grid, block, st, pdl);
+	if (pipe == 2 && phase == 1 && V > 1)                        /* aligned accesses + warp shuffles (lbm_tuning.neighbour == 0) */
+		return launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 2>, p, grid, block, st, pdl);
 	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 0>, p, grid, block, st, pdl)
 	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 0>, p, grid, block, st, pdl);
 }
@@ -384,8 +386,9 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			/* x: the vectors of one row; y: rows, capped (grid-stride) by ctas_per_sm and by the 65535 limit */
 			const unsigned gx = (ncols / (unsigned)V + block - 1) / block;
 			unsigned gy = rows;
-			const int pipe = c->tune.rows_per_thread >= 2 && V <= 2;     /* wider vectors: the second register set spills */
+			int pipe = c->tune.rows_per_thread >= 2 && V <= 2;           /* wider vectors: the second register set spills */
 			if (pipe) gy = (rows + (unsigned)c->tune.rows_per_thread - 1) / (unsigned)c->tune.rows_per_thread;
+			else if (c->tune.neighbour == 0) pipe = 2;
 			if (c->tune.ctas_per_sm > 0) {
 				const unsigned cap = (unsigned)(sm_count(c->cfg.device) * c->tune.ctas_per_sm) / gx;
 				if (gy > cap) gy = cap < 1 ? 1 : cap;

@@ -554,6 +554,96 @@ __device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, 
 	}
 }
 
+// ---------------------------------------------------------------------------
+// Phase 1 with every global access an ALIGNED vector (V > 1): the element a shifted stream needs from column
+// j0-1 / j0+V is the adjacent lane's aligned load (warp shuffle), and the element a thread owes to the
+// adjacent lane's aligned vector travels the same way before the store; only the lanes at a warp edge or at
+// an end of the row's column range fall back to one scalar access.  Safe in place: the shuffled element
+// belongs to the receiving thread's own site set, and a warp issues its loads before its stores.
+// All 32 lanes must call these (idle lanes shadow the last vector of the range and do not store).
+// ---------------------------------------------------------------------------
+template <typename T, int V>
+__device__ __forceinline__ void aa_load_shf(const StepParams<T> &p, int r, int j0, bool edge_l, bool edge_r, T (&f)[9][V])
+{
+	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;
+	const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
+	const int jr = j0 + V == p.ny ? 0 : j0 + V;
+	const T *lrow[3] = {own - p.ldy, own, own + p.ldy};
+#pragma unroll
+	for (int s = 0; s < 9; s++) {
+		const T *b = lrow[pull_di(s) + 1] + (size_t)s * p.plane;
+		T al[V];
+		ldc<V>(b + j0, al);
+		if (pull_dj(s) == 0) {
+#pragma unroll
+			for (int k = 0; k < V; k++) f[s][k] = al[k];
+		} else if (pull_dj(s) < 0) {
+			T nb = __shfl_up_sync(0xffffffffu, al[V - 1], 1);
+			if (edge_l) nb = b[jl];
+			f[s][0] = nb;
+#pragma unroll
+			for (int k = 1; k < V; k++) f[s][k] = al[k - 1];
+		} else {
+			T nb = __shfl_down_sync(0xffffffffu, al[0], 1);
+			if (edge_r) nb = b[jr];
+			f[s][V - 1] = nb;
+#pragma unroll
+			for (int k = 0; k < V - 1; k++) f[s][k] = al[k + 1];
+		}
+	}
+}
+
+template <typename T, int V>
+__device__ __forceinline__ void aa_store_shf(const StepParams<T> &p, int r, int j0, bool edge_l, bool edge_r, bool active, const T (&o)[9][V])
+{
+	T *const own = p.dst + (size_t)(r + 1) * p.ldy;
+	const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
+	const int jr = j0 + V == p.ny ? 0 : j0 + V;
+	T *srow[3];
+	size_t spl[3];
+	srow[1] = own;              spl[1] = p.plane;
+	if (r == 0) { srow[0] = p.dn_halo - p.ldy; spl[0] = p.dn_plane; } else { srow[0] = own - p.ldy; spl[0] = p.plane; }
+	if (r == p.nxl - 1) { srow[2] = p.up_halo + p.ldy; spl[2] = p.up_plane; } else { srow[2] = own + p.ldy; spl[2] = p.plane; }
+#pragma unroll
+	for (int k = 0; k < 9; k++) {
+		T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
+		const T (&v)[V] = o[opposite(k)];
+		if (pull_dj(k) == 0) {
+			if (active) stv<0, V>(b + j0, v);
+		} else if (pull_dj(k) < 0) {                         // my values belong at columns j0-1 .. j0+V-2
+			const T recv = __shfl_down_sync(0xffffffffu, v[0], 1);   // the right lane's first value: my vector's last column
+			if (active) {
+				if (!edge_r) {
+					T w[V];
+#pragma unroll
+					for (int m = 0; m < V - 1; m++) w[m] = v[m + 1];
+					w[V - 1] = recv;
+					stv<0, V>(b + j0, w);
+				} else {
+#pragma unroll
+					for (int m = 1; m < V; m++) b[j0 + m - 1] = v[m];
+				}
+				if (edge_l) b[jl] = v[0];
+			}
+		} else {                                             // my values belong at columns j0+1 .. j0+V
+			const T recv = __shfl_up_sync(0xffffffffu, v[V - 1], 1);  // the left lane's last value: my vector's first column
+			if (active) {
+				if (!edge_l) {
+					T w[V];
+					w[0] = recv;
+#pragma unroll
+					for (int m = 1; m < V; m++) w[m] = v[m - 1];
+					stv<0, V>(b + j0, w);
+				} else {
+#pragma unroll
+					for (int m = 0; m < V - 1; m++) b[j0 + m + 1] = v[m];
+				}
+				if (edge_r) b[jr] = v[V - 1];
+			}
+		}
+	}
+}
+
 // row ranges of the wavefront schedule may wrap (r1 > nxl)
 template <typename T> __device__ __forceinline__ int aa_row(const StepParams<T> &p, uint32_t rr)
 {
@@ -584,8 +674,24 @@ stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 	int j0 = p.jmin + (int)jv * V;
 	if (j0 >= p.ny) j0 -= p.ny;                              // column ranges of the 2-D wavefront schedule may wrap (jmax > ny)
 	asm volatile("griddepcontrol.wait;" ::: "memory");
+	if constexpr (PIPE == 2 && PHASE == 1 && V > 1) {            // PIPE == 2: the aligned-access (warp shuffle) phase 1
+		const bool active = jv < nvec;
+		const uint32_t jc = active ? jv : nvec - 1;              // idle lanes shadow the last vector (loads stay legal)
+		int jj = p.jmin + (int)jc * V;
+		if (jj >= p.ny) jj -= p.ny;
+		const uint32_t lane = threadIdx.x & 31u;
+		const bool edge_l = lane == 0 || jc == 0, edge_r = lane == 31 || jc >= nvec - 1;
+		for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
+			const int r = aa_row(p, rr);
+			T f[9][V], o[9][V];
+			aa_load_shf<T, V>(p, r, jj, edge_l, edge_r, f);
+			relax_sites<T, V>(p, f, o, r, jj, p.tail_source);
+			aa_store_shf<T, V>(p, r, jj, edge_l, edge_r, active, o);
+		}
+		return;
+	}
 	if (jv >= nvec) return;
-	if constexpr (PIPE == 0) {
+	if constexpr (PIPE != 1) {
 		for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
 			const int r = aa_row(p, rr);
 			T f[9][V], o[9][V];

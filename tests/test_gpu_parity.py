@@ -55,7 +55,9 @@ ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), 
            "inplace+tb+graph+pdl": dict(inplace=1, tb_depth=6, tb_rows=5, graph=1, pdl=1),
            "inplace+tb+pipe": dict(inplace=1, tb_depth=8, tb_rows=12, rows_per_thread=3, vec=1, graph=1, pdl=1),
            # 2-D tiles: column strips as well as row bands (falls back to bands where ny is not a multiple of 8)
-           "inplace+tb2d": dict(inplace=1, tb_depth=4, tb_rows=16, tb_cols=256, graph=1, pdl=1)}
+           "inplace+tb2d": dict(inplace=1, tb_depth=4, tb_rows=16, tb_cols=256, graph=1, pdl=1),
+           # phase 1 with aligned vector accesses only, +-1 column elements exchanged by warp shuffles
+           "inplace+shuffle": dict(inplace=1, neighbour=0), "inplace+shuffle+tb2d": dict(inplace=1, neighbour=0, vec=2, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1)}
 
 
 def _split(engine_kw):
@@ -69,8 +71,9 @@ def _split(engine_kw):
 @pytest.mark.parametrize("name", list(cases.CASES))
 def test_cuda_matches_reference_golden(name, engine):
     c, g = cases.CASES[name], GOLDEN[name]
-    if engine in ("pdl", "graph") and c["steps"] > 1000:
-        pytest.skip("10,000-step cases: default, persistent and graph+pdl engines only")
+    if engine in ("pdl", "graph", "inplace+tb2d", "inplace+shuffle+tb2d") and c["steps"] > 1000:
+        pytest.skip("10,000-step cases: not under the plain pdl/graph engines, nor under the deliberately tiny 2-D tiles "
+                    "(tens of millions of launches); the in-place defaults cover temporal blocking at full length")
     fA, walls = cases.make_inputs(name)
     ctor, tune = _split(ENGINES[engine])
     with _lattice(c, **ctor) as lat:
@@ -156,7 +159,8 @@ def test_every_kernel_variant_is_bit_identical(prec):
     vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
     with _lattice(c, inplace=True) as lat:
         for v in vecs:
-            for extra in (dict(block=128), dict(block=256, ctas_per_sm=2), dict(block=64, pdl=1, graph=2), dict(block=512, ctas_per_sm=1, pdl=1)):
+            for extra in (dict(block=128), dict(block=256, ctas_per_sm=2), dict(block=64, pdl=1, graph=2), dict(block=512, ctas_per_sm=1, pdl=1),
+                          dict(block=128, neighbour=0), dict(block=96, neighbour=0, ctas_per_sm=1), dict(block=32, neighbour=0, tb_depth=4, tb_rows=11, tb_cols=40)):
                 tune = dict(dict(vec=v, neighbour=1, hints=0, ctas_per_sm=0, persistent=0, pdl=0, graph=0), **extra)
                 lat.set_tuning(**tune)
                 lat.upload(fA, walls)

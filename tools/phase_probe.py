@@ -14,11 +14,11 @@ for prec, nx, ny in (("dp", 400, 2000), ("sp", 400, 4000)):
     with Lattice(nx, ny, prec, inplace=True) as lat:
         lat.InitializeArrays()
         lat.run(10)
-        for vec in ((1, 2) if prec == "dp" else (2, 4)):
-            for rpt in (0, 2, 4, 8):
-                if vec == 4 and rpt:
+        for vec in ((1, 2, 4) if prec == "dp" else (2, 4, 8)):
+            for rpt in (0, -1):                       # -1: aligned accesses + warp shuffles (neighbour = 0)
+                if vec == 1 and rpt:
                     continue
-                lat.set_tuning(vec=vec, rows_per_thread=rpt, pdl=1, graph=0, tb_depth=0)
+                lat.set_tuning(vec=vec, rows_per_thread=max(rpt, 0), neighbour=0 if rpt < 0 else 1, pdl=1, graph=0, tb_depth=0)
                 for phase in (0, 1):
                     n = 3000
                     for _ in range(200):
