@@ -189,6 +189,8 @@ typedef struct {
 	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
 	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 32 KB
 	                     row segments only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
+	int vec_phase1;   /* in-place kernels: sites per thread in phase 1 (the neighbour-access phase); 0 = same as vec.  SP runs
+	                     phase 1 fastest at 2 and phase 2 at 4 (profiles/r01_run17/phase_probe.log) */
 	int rows_per_thread; /* in-place kernels: >= 2 = each thread walks that many rows of its launch and loads the
 	                     populations of its next row before relaxing the current one (software pipelining against
 	                     L2 latency); 0/1 = one row per thread */

@@ -266,6 +266,8 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) {
 			c->tune.tb_depth = k;
 			if (sizeof(real_t) == 4) c->tune.vec = 2;                /* SP 800x4000: 98.7 (vec 2) vs 83.8 GLUPS (vec 4), profiles/r01_run11 */
+		} else if (sizeof(real_t) == 4) {
+			c->tune.vec_phase1 = 2;                                  /* L2-resident SP: phase 1 20.6 us at vec 2 vs 22.5 at vec 4 (phase 2: 16.3 vs 14.8) */
 		}
 	}
 	*out = c;
@@ -370,6 +372,7 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 	}
 	if (c->vw > 1 && c->nyvec > 0) {
 		int V = c->tune.vec;
+		if (c->inplace && src == 0 && c->tune.vec_phase1) V = c->tune.vec_phase1;
 		if (V > c->vw) V = c->vw;
 		const unsigned block = (unsigned)c->tune.block;
 		const unsigned long long total = (unsigned long long)rows * (unsigned)(c->nyvec / V);
@@ -1115,6 +1118,8 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
 	if (n.tb_rows < 0 || n.tb_cols < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d, tb_cols %d", n.tb_rows, n.tb_cols);
+	if (n.vec_phase1 != 0 && ((n.vec_phase1 != 1 && n.vec_phase1 != 2 && n.vec_phase1 != 4 && n.vec_phase1 != 8) || n.vec_phase1 > vmax))
+		return fail(LBM_ERR_ARG, "lbm_set_tuning: vec_phase1 %d", n.vec_phase1);
 	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");

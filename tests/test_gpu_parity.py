@@ -160,8 +160,9 @@ def test_every_kernel_variant_is_bit_identical(prec):
     with _lattice(c, inplace=True) as lat:
         for v in vecs:
             for extra in (dict(block=128), dict(block=256, ctas_per_sm=2), dict(block=64, pdl=1, graph=2), dict(block=512, ctas_per_sm=1, pdl=1),
-                          dict(block=128, neighbour=0), dict(block=96, neighbour=0, ctas_per_sm=1), dict(block=32, neighbour=0, tb_depth=4, tb_rows=11, tb_cols=40)):
-                tune = dict(dict(vec=v, neighbour=1, hints=0, ctas_per_sm=0, persistent=0, pdl=0, graph=0), **extra)
+                          dict(block=128, neighbour=0), dict(block=96, neighbour=0, ctas_per_sm=1), dict(block=32, neighbour=0, tb_depth=4, tb_rows=11, tb_cols=40),
+                          dict(block=128, vec_phase1=2 if v != 2 else 1), dict(block=64, vec_phase1=vecs[-1], neighbour=0, pdl=1, graph=1)):
+                tune = dict(dict(vec=v, neighbour=1, hints=0, ctas_per_sm=0, persistent=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0, vec_phase1=0), **extra)
                 lat.set_tuning(**tune)
                 lat.upload(fA, walls)
                 lat.run(4)
