@@ -10,7 +10,9 @@
  *     SCENE: 0 = InitializeArrays (channel + barrier, LB.c:559-578)
  *            1 = channel + disc obstacle (BASELINE config 3: centre (NX/2, NY/5), radius NX/10)
  *     DUMP_EVERY > 0 writes data/<step>.csv like SAVELATTICE (LB.c:155-159; data/ must exist)
- *     INPLACE = 1: one buffer per slab instead of fA/fB (lbm_config.inplace), same fA after every DoTimeStep
+ *     INPLACE = 1 (default): one buffer per slab instead of fA/fB (lbm_config.inplace) -- this main never reads fB
+ *            (LB.c:152,157,172-173 take fA), fA after every DoTimeStep is bit-identical, and the steps between two
+ *            observation points run temporally blocked in L2; 0 = the reference's fA/fB pair
  * Defaults reproduce the shipped program: 400 x 2000, 10000 steps.
  */
 #ifdef LBM_DRIVER_FLOAT
@@ -92,7 +94,7 @@ static int reynolds(real_t *re)
 
 int main(int argc, char **argv)
 {
-	int scene_id = 0, dump_every = 0, inplace = 0;
+	int scene_id = 0, dump_every = 0, inplace = 1;
 	if (argc >= 4) { NX = atoi(argv[1]); NY = atoi(argv[2]); NTIMESTEPS = atoi(argv[3]); }
 	if (argc >= 5) NGPU = atoi(argv[4]);
 	if (argc >= 6) scene_id = atoi(argv[5]);
