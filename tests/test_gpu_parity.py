@@ -358,7 +358,7 @@ def test_c_driver_prints_reference_reynolds():
     """driver/main.c (the reference's main over the C ABI) on the shipped scenario: the final line's
     Re must be the compiled reference's value to all printed digits (LB.c:173, %.10le)."""
     for tag, case, extra in (("dp", "builtin_dp_10000", []), ("sp", "builtin_sp_10000", []),
-                             ("dp", "builtin_dp_10000", ["1", "0", "0", "1"]), ("sp", "builtin_sp_10000", ["1", "0", "0", "1"])):
+                             ("dp", "builtin_dp_10000", ["1", "0", "0", "0"]), ("sp", "builtin_sp_10000", ["1", "0", "0", "0"])):   # INPLACE=0: fA/fB pair
         exe = os.path.join(ROOT, "driver", f"lbm_b200_{tag}")
         out = subprocess.run([exe, "400", "2000", "10000"] + extra, capture_output=True, text=True, timeout=300)
         assert out.returncode == 0, out.stderr
