@@ -178,7 +178,12 @@ def roofline(prec, sites, timesteps_total, kernel_launches, total_ms, peak, peak
     achieved = bytes_per_launch / per_launch_s / 1e9
     if kernel_launches < timesteps_total:
         kernel = "lbm::stream_collide_persistent_kernel"
-    return {"bound": "hbm", "kernel": kernel,
+    note = None
+    if kernel_launches > timesteps_total:      # temporal blocking: several tile launches per timestep
+        note = ("HBM is the roofline the path is specified against (144/72 B per site update); with temporal blocking in L2 the tiles are "
+                "re-used for k timesteps, measured DRAM traffic ('traffic', ncu without cache flushes) is a fraction of the algorithmic bytes, "
+                "frac > 1 is expected and the kernel is bound by instruction issue (DESIGN.md, 'In-place streaming')")
+    return {"bound": "hbm", "kernel": kernel, "note": note,
             "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
             "traffic": ncu_traffic(traffic_key or prec), "algorithmic_bytes_per_launch": int(round(bytes_per_launch)),
             "timesteps_per_launch": round(timesteps_total / kernel_launches, 4),
