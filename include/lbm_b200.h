@@ -170,7 +170,7 @@ int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary strea
 /* ---- tuning / accounting ---- */
 typedef struct {
 	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = by lattice size (DP: 1 up to 16 Mi sites, else 4; SP: 4) */
-	int block;        /* threads per CTA; 0 = default */
+	int block;        /* threads per CTA; 0 = default (the SP in-place kernels run at most 256) */
 	int neighbour;    /* 0 = warp shuffle for the +-1 column element, 1 = direct load */
 	int hints;        /* 0 = default caching, 1 = L1::no_allocate loads + .cs stores */
 	int ctas_per_sm;  /* >0: cap the grid at SMs*ctas_per_sm CTAs (grid-stride), 0 = one pass */
@@ -189,8 +189,7 @@ typedef struct {
 	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
 	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 32 KB
 	                     row segments only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
-	int vec_phase1;   /* in-place kernels: sites per thread in phase 1 (the neighbour-access phase); 0 = same as vec.  SP runs
-	                     phase 1 fastest at 2 and phase 2 at 4 (profiles/r01_run17/phase_probe.log) */
+	int vec_phase1;   /* in-place kernels: sites per thread in phase 1 (the neighbour-access phase); 0 = same as vec */
 	int rows_per_thread; /* in-place kernels: >= 2 = each thread walks that many rows of its launch and loads the
 	                     populations of its next row before relaxing the current one (software pipelining against
 	                     L2 latency); 0/1 = one row per thread */

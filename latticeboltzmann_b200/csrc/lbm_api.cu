@@ -266,8 +266,6 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) {
 			c->tune.tb_depth = k;
 			if (sizeof(real_t) == 4) c->tune.vec = 2;                /* SP 800x4000: 98.7 (vec 2) vs 83.8 GLUPS (vec 4), profiles/r01_run11 */
-		} else if (sizeof(real_t) == 4) {
-			c->tune.vec_phase1 = 2;                                  /* L2-resident SP: phase 1 20.6 us at vec 2 vs 22.5 at vec 4 (phase 2: 16.3 vs 14.8) */
 		}
 	}
 	*out = c;
@@ -374,7 +372,8 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		int V = c->tune.vec;
 		if (c->inplace && src == 0 && c->tune.vec_phase1) V = c->tune.vec_phase1;
 		if (V > c->vw) V = c->vw;
-		const unsigned block = (unsigned)c->tune.block;
+		unsigned block = (unsigned)c->tune.block;
+		if (c->inplace && sizeof(real_t) == 4 && block > 256) block = 256;      /* launch bounds of the SP in-place kernels */
 		const unsigned long long total = (unsigned long long)rows * (unsigned)(c->nyvec / V);
 		unsigned long long grid = (total + block - 1) / block;
 		if (c->tune.ctas_per_sm > 0) {

@@ -661,7 +661,10 @@ template <typename T> __device__ __forceinline__ int aa_row(const StepParams<T> 
 #ifdef LBM_AA_MINB      /* experiment builds (tools/): 128-thread CTAs, at least LBM_AA_MINB of them per SM */
 #define LBM_AA_BOUNDS __launch_bounds__(128, LBM_AA_MINB)
 #else
-#define LBM_AA_BOUNDS __launch_bounds__(512)
+// SP: CTAs of at most 256 threads, four of them per SM -> 64 registers.  Measured on the L2-resident 400x4000 lattice
+// (profiles/r01_run24/occ_probe_sp.log): phase 1 at vec 4 drops from 104 registers / 22.4 us to 64 / 17.7 us, the
+// run from 113.2 to 119.7 GLUPS.  DP (54-58 registers at vec 1) gains nothing from a cap (profiles/r01_run12).
+#define LBM_AA_BOUNDS __launch_bounds__(sizeof(T) == 4 ? 256 : 512, sizeof(T) == 4 ? 4 : 0)
 #endif
 template <typename T, int V, int PHASE, int PIPE>
 __global__ void LBM_AA_BOUNDS
