@@ -193,6 +193,12 @@ typedef struct {
 	int rows_per_thread; /* in-place kernels: >= 2 = each thread walks that many rows of its launch and loads the
 	                     populations of its next row before relaxing the current one (software pipelining against
 	                     L2 latency); 0/1 = one row per thread */
+	int dataflow;     /* in-place single-slab contexts with temporal blocking in full-width row bands: >= 1 = ONE launch per
+	                     macro-step instead of one per (band, level).  The launches of the schedule are cut into items of one
+	                     row x (block * vec * dataflow) columns, taken by a grid of co-resident CTAs in schedule order; an
+	                     item of level s starts when rows i-1, i, i+1 have finished level s-1 (per-row counters), which is
+	                     all the kernel boundaries guaranteed.  No drain/refill between the short launches.  With it,
+	                     hints = 1 selects L1-cached loads (default: ld.global.cg).  0 = off */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
@@ -204,7 +210,8 @@ long long lbm_kernel_launches(lbm_ctx *ctx);
  * seam (slabs of a multi-slab ring, multi != 0): bit 0 = wait for both neighbours' previous event before this
  * launch, bit 1 = announce this slab's event after it.  *depth_used = the depth used (single slab: clamped to the
  * ring, 0 = lattice too small, plain stepping).  Returns the number of launches (which may exceed cap; only cap
- * entries are written), -1 on bad arguments. */
+ * entries are written), -1 on bad arguments.  multi == 2: the order in which the dataflow kernel (lbm_tuning.dataflow)
+ * of a single slab takes the same launches. */
 int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
 
 #ifdef __cplusplus

@@ -90,6 +90,13 @@ struct lbm_ctx {
 	cudaGraphExec_t wf_exec;     // captured wavefront macro-step (wf_k timesteps, bands of wf_h rows)
 	long long wf_launches;       // kernels in that graph
 	int in_wavefront;            // set while run_wavefront enqueues (step kernels may then use PDL on slabs too)
+	/* dataflow kernel (lbm_tuning.dataflow): one launch per macro-step */
+	int *df_cnt;                 // [df_cnt_ints] finished chunks per (level, row)
+	size_t df_cnt_ints;
+	DfLaunch *df_list[2];        // device launch lists: [0] a full macro-step with every tail source (cached), [1] a run's last one
+	size_t df_list_cap[2];
+	int df_nlaunch;              // of df_list[0]; 0 = not built for the current tuning
+	unsigned df_nitems;
 };
 
 namespace {
@@ -112,6 +119,7 @@ void drop_graph(lbm_ctx *c)
 	c->graph_pairs = 0;
 	if (c->wf_exec) cudaGraphExecDestroy(c->wf_exec);
 	c->wf_exec = nullptr;
+	c->df_nlaunch = 0;
 }
 
 int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_OK; }
@@ -287,6 +295,9 @@ int lbm_destroy(lbm_ctx *c)
 	drop_graph(c);
 	if (c->flags) cudaFree(c->flags);
 	if (c->progress) cudaFree(c->progress);
+	if (c->df_cnt) cudaFree(c->df_cnt);
+	for (int i = 0; i < 2; i++)
+		if (c->df_list[i]) cudaFree(c->df_list[i]);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
 	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
 	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -703,6 +714,140 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 	return LBM_OK;
 }
 
+/* ---- dataflow kernel: a whole macro-step in one launch (single slab, whole-row pieces) ---- */
+/* Its item order: tb_for_each_launch's, except that inverted-pyramid level s is issued right after level s-1 of the
+ * last other row piece instead of after all of that piece's levels.  Valid: inverted level s reads rows
+ * [nx-s-1, nx+s+1) of level s-1, which lie in that piece's, the pyramid's and its own level s-1 -- all issued
+ * earlier.  The short ring-closing levels then run beside the big launches instead of as a serial chain at the end. */
+bool df_plan_ok(const TbPlan &pl)
+{
+	return pl.k >= 2 && pl.cols.npieces == 1 && pl.cols.piece[0].type == TB_WHOLE && pl.rows.piece[0].type != TB_WHOLE;
+}
+
+template <typename F> int df_for_each_launch(const TbPlan &pl, int kk, F visit)
+{
+	const int np = pl.rows.npieces;
+	const int inv = (np >= 2 && pl.rows.piece[np - 1].type == TB_INVERTED) ? np - 1 : -1;
+	int rc, r0, r1;
+	for (int ri = 0; ri < np; ri++) {
+		if (ri == inv) continue;
+		const bool carries_inv = inv >= 0 && ri == inv - 1;
+		for (int s = 0; s < kk; s++) {
+			if (carries_inv) {
+				tb_range(pl.rows, pl.rows.piece[inv], s, &r0, &r1);
+				if (r1 > r0 && (rc = visit(s, r0, r1))) return rc;
+			}
+			tb_range(pl.rows, pl.rows.piece[ri], s, &r0, &r1);
+			if (r1 > r0 && (rc = visit(s, r0, r1))) return rc;
+		}
+	}
+	return 0;
+}
+
+/* device copy of the launch list of one macro-step of kk levels starting at timestep t0 (slot 0: cached full macro-step) */
+int df_upload_list(lbm_ctx *c, int slot, const TbPlan &pl, int kk, int t0, int nsteps, int chunks, int *nlaunch, unsigned *nitems)
+{
+	std::vector<DfLaunch> l;
+	unsigned long long first = 0;
+	df_for_each_launch(pl, kk, [&](int s, int r0, int r1) {
+		DfLaunch d;
+		d.level = s; d.r0 = r0 >= c->nxl ? r0 - c->nxl : r0; d.rows = r1 - r0;
+		d.tail_source = t0 + s != nsteps - 1;
+		d.first = (unsigned)first;
+		first += (unsigned long long)d.rows * (unsigned)chunks;
+		l.push_back(d);
+		return 0;
+	});
+	if (first >= (1ull << 31)) return fail(LBM_ERR_ARG, "dataflow: %llu items in a macro-step", first);
+	if (l.size() > c->df_list_cap[slot]) {
+		if (c->df_list[slot]) CK(cudaFree(c->df_list[slot]));
+		c->df_list[slot] = nullptr; c->df_list_cap[slot] = 0;
+		CK(cudaMalloc(&c->df_list[slot], l.size() * sizeof(DfLaunch)));
+		c->df_list_cap[slot] = l.size();
+	}
+	CK(cudaMemcpyAsync(c->df_list[slot], l.data(), l.size() * sizeof(DfLaunch), cudaMemcpyHostToDevice, c->stream[0]));   /* pageable: staged before return */
+	*nlaunch = (int)l.size(); *nitems = (unsigned)first;
+	return LBM_OK;
+}
+
+template <int V>
+int launch_dataflow_v(lbm_ctx *c, const StepParams<real_t> &p, const DfParams &q, unsigned block, cudaStream_t st)
+{
+	const void *kern = c->tune.hints ? (const void *)stream_collide_aa_dataflow_kernel<real_t, V, false>
+	                                 : (const void *)stream_collide_aa_dataflow_kernel<real_t, V, true>;
+	int occ = 0;
+	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, (int)block, 0));
+	if (c->tune.ctas_per_sm > 0 && occ > c->tune.ctas_per_sm) occ = c->tune.ctas_per_sm;
+	if (occ < 1) return fail(LBM_ERR_CUDA, "dataflow kernel does not fit an SM at block %u", block);
+	unsigned long long grid = (unsigned long long)occ * sm_count(c->cfg.device);
+	if (grid > q.nitems) grid = q.nitems;
+	StepParams<real_t> pp = p;
+	DfParams qq = q;
+	void *args[] = {(void *)&pp, (void *)&qq};
+	CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(block), args, 0, st));
+	c->launches++;
+	return LBM_OK;
+}
+
+int launch_dataflow(lbm_ctx *c, int slot, int nlaunch, unsigned nitems, int levels, int chunks, int iters, unsigned block, cudaStream_t st)
+{
+	StepParams<real_t> p = make_params(c, 0, 0, c->nxl, 1);
+	DfParams q;
+	q.list = c->df_list[slot]; q.nlaunch = nlaunch; q.nitems = nitems; q.chunks = chunks; q.iters = iters;
+	q.cnt = c->df_cnt; q.levels = levels;
+	q.abort = c->progress + PROGRESS_SLOTS;
+	q.timeout_ns = 10ull * 1000 * 1000 * 1000;
+	CK(cudaMemsetAsync(c->df_cnt, 0, (size_t)levels * c->nxl * sizeof(int), st));
+	c->launches_persistent = 1;                                  /* lbm_sync then looks at the abort word */
+	int V = c->tune.vec;
+	if (V > c->vw) V = c->vw;
+	switch (V) {
+	case 1: return launch_dataflow_v<1>(c, p, q, block, st);
+	case 2: return launch_dataflow_v<2>(c, p, q, block, st);
+	case 4: return launch_dataflow_v<4>(c, p, q, block, st);
+#ifdef LBM_FLOAT
+	case 8: return launch_dataflow_v<8>(c, p, q, block, st);
+#endif
+	}
+	return fail(LBM_ERR_ARG, "launch_dataflow: vec %d", V);
+}
+
+int run_dataflow(lbm_ctx *c, int nsteps, const TbPlan &pl)
+{
+	int rc;
+	const int k = pl.k;
+	int V = c->tune.vec;
+	if (V > c->vw) V = c->vw;
+	unsigned block = (unsigned)c->tune.block;
+	if (block > (sizeof(real_t) == 4 ? 256u : 128u)) block = sizeof(real_t) == 4 ? 256u : 128u;    /* launch bounds of the kernel */
+	const int iters = c->tune.dataflow;
+	const unsigned cw = block * (unsigned)iters;                 /* vectors per chunk */
+	const int chunks = (int)(((unsigned)(c->ny / V) + cw - 1) / cw);
+	const size_t need = (size_t)k * c->nxl;
+	if (need > c->df_cnt_ints) {
+		if (c->df_cnt) CK(cudaFree(c->df_cnt));
+		c->df_cnt = nullptr; c->df_cnt_ints = 0;
+		CK(cudaMalloc(&c->df_cnt, need * sizeof(int)));
+		c->df_cnt_ints = need;
+	}
+	CK(cudaMemsetAsync(c->progress + PROGRESS_SLOTS, 0, sizeof(int), c->stream[0]));
+	int t = 0;
+	if (nsteps - k >= k) {                                       /* full macro-steps, every level with its tail source */
+		if (!c->df_nlaunch && (rc = df_upload_list(c, 0, pl, k, 0, 1 << 30, chunks, &c->df_nlaunch, &c->df_nitems))) return rc;
+		for (; nsteps - k - t >= k; t += k)
+			if ((rc = launch_dataflow(c, 0, c->df_nlaunch, c->df_nitems, k, chunks, iters, block, c->stream[0]))) return rc;
+	}
+	while (t < nsteps) {                                         /* the last one or two: the run's last level leaves A un-sourced */
+		const int kk = nsteps - t < k ? nsteps - t : k;
+		int nl = 0;
+		unsigned ni = 0;
+		if ((rc = df_upload_list(c, 1, pl, kk, t, nsteps, chunks, &nl, &ni))) return rc;
+		if ((rc = launch_dataflow(c, 1, nl, ni, kk, chunks, iters, block, c->stream[0]))) return rc;
+		t += kk;
+	}
+	return LBM_OK;
+}
+
 int run_wavefront(lbm_ctx *c, int nsteps)
 {
 	int rc;
@@ -715,6 +860,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 			if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
 		return LBM_OK;
 	}
+	if (c->tune.dataflow > 0 && c->sync_mode == SYNC_SELF && c->vw > 1 && c->nyvec == c->ny && df_plan_ok(pl)) return run_dataflow(c, nsteps, pl);
 	int t = 0;
 	struct Scope { lbm_ctx *c; Scope(lbm_ctx *c_) : c(c_) { c->in_wavefront = 1; } ~Scope() { c->in_wavefront = 0; } } scope(c);
 	if (c->tune.graph > 0 && nsteps - k >= k && c->sync_mode == SYNC_SELF) {      /* slabs: the epochs of wait/signal change per launch */
@@ -899,7 +1045,7 @@ int lbm_sync(lbm_ctx *c)
 	if (c->sync_mode == SYNC_SELF && c->launches_persistent) {
 		int ab = 0;
 		CK(cudaMemcpy(&ab, c->progress + PROGRESS_SLOTS, sizeof ab, cudaMemcpyDeviceToHost));
-		if (ab) return fail(LBM_ERR_STATE, "persistent kernel: neighbour wait timed out");
+		if (ab) return fail(LBM_ERR_STATE, "persistent / dataflow kernel: a dependency wait timed out");
 	}
 	if (c->sync_mode == SYNC_FLAGS) {
 		int fl[4];
@@ -1120,6 +1266,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.vec_phase1 != 0 && ((n.vec_phase1 != 1 && n.vec_phase1 != 2 && n.vec_phase1 != 4 && n.vec_phase1 != 8) || n.vec_phase1 > vmax))
 		return fail(LBM_ERR_ARG, "lbm_set_tuning: vec_phase1 %d", n.vec_phase1);
 	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
+	if (n.dataflow < 0 || n.dataflow > 64) return fail(LBM_ERR_ARG, "lbm_set_tuning: dataflow %d (0..64)", n.dataflow);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");
 	drop_graph(c);
@@ -1140,10 +1287,20 @@ int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb
 	const int per128 = 128 / (int)sizeof(real_t);
 	const int ldy = ((ny + per128 - 1) / per128) * per128;
 	static thread_local TbPlan pl;
-	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi != 0, tb_depth, tb_rows, tb_cols);
+	if (multi < 0 || multi > 2) { fail(LBM_ERR_ARG, "lbm_tb_schedule: multi %d", multi); return -1; }
+	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi == 1, tb_depth, tb_rows, tb_cols);
 	if (depth_used) *depth_used = pl.k;
 	if (pl.k < 2) return 0;
 	int n = 0;
+	if (multi == 2) {                                            /* item order of the dataflow kernel */
+		if (!df_plan_ok(pl)) { fail(LBM_ERR_ARG, "lbm_tb_schedule: the dataflow kernel takes full-width row bands only"); return -1; }
+		df_for_each_launch(pl, pl.k, [&](int s, int r0, int r1) {
+			if (n < cap) { int *o = launches + 6 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = o[4] = o[5] = 0; }
+			n++;
+			return 0;
+		});
+		return n;
+	}
 	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1, int seam) {
 		if (n < cap) { int *o = launches + 6 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; o[5] = seam; }
 		n++;

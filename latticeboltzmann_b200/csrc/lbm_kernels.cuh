@@ -436,21 +436,27 @@ stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 // memory, or this slab itself when P == 1); phase 2 pushes the three halo speeds like the A/B
 // kernel does.  Same bytes over NVLink per two steps as A/B.
 // ---------------------------------------------------------------------------
-template <int V> __device__ __forceinline__ void ldc(const double *p, double (&v)[V])
+// CG: ld.global.cg (L2 only) -- for the dataflow kernel, whose CTAs read what other SMs wrote during the same launch
+template <bool CG, typename X> __device__ __forceinline__ X ld_coh(const X *p)
 {
-	if constexpr (V == 1) v[0] = *p;
+	if constexpr (CG) return __ldcg(p);
+	else return *p;
+}
+template <int V, bool CG = false> __device__ __forceinline__ void ldc(const double *p, double (&v)[V])
+{
+	if constexpr (V == 1) v[0] = ld_coh<CG>(p);
 	else {
 #pragma unroll
-		for (int k = 0; k < V; k += 2) { const double2 t = *reinterpret_cast<const double2 *>(p + k); v[k] = t.x; v[k + 1] = t.y; }
+		for (int k = 0; k < V; k += 2) { const double2 t = ld_coh<CG>(reinterpret_cast<const double2 *>(p + k)); v[k] = t.x; v[k + 1] = t.y; }
 	}
 }
-template <int V> __device__ __forceinline__ void ldc(const float *p, float (&v)[V])
+template <int V, bool CG = false> __device__ __forceinline__ void ldc(const float *p, float (&v)[V])
 {
-	if constexpr (V == 1) v[0] = *p;
-	else if constexpr (V == 2) { const float2 t = *reinterpret_cast<const float2 *>(p); v[0] = t.x; v[1] = t.y; }
+	if constexpr (V == 1) v[0] = ld_coh<CG>(p);
+	else if constexpr (V == 2) { const float2 t = ld_coh<CG>(reinterpret_cast<const float2 *>(p)); v[0] = t.x; v[1] = t.y; }
 	else {
 #pragma unroll
-		for (int k = 0; k < V; k += 4) { const float4 t = *reinterpret_cast<const float4 *>(p + k); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
+		for (int k = 0; k < V; k += 4) { const float4 t = ld_coh<CG>(reinterpret_cast<const float4 *>(p + k)); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
 	}
 }
 // V values to columns (j0-1 .. j0+V-2) [DJ < 0, first one wraps to jl] or (j0+1 .. j0+V) [DJ > 0, last one wraps to jr]
@@ -482,13 +488,13 @@ template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(
 }
 
 // the nine populations the V sites (r, j0..j0+V-1) relax this step
-template <typename T, int V, int PHASE>
+template <typename T, int V, int PHASE, bool CG = false>
 __device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T (&f)[9][V])
 {
 	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;    // p.src == p.dst
 	if constexpr (PHASE == 2) {
 #pragma unroll
-		for (int s = 0; s < 9; s++) ldc<V>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
+		for (int s = 0; s < 9; s++) ldc<V, CG>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
 	} else {
 		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;          // LB.c:337-338
 		const int jr = j0 + V == p.ny ? 0 : j0 + V;
@@ -497,19 +503,19 @@ __device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T
 		for (int s = 0; s < 9; s++) {
 			const T *b = lrow[pull_di(s) + 1] + (size_t)s * p.plane;
 			if constexpr (V == 1) {
-				f[s][0] = b[pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0];
+				f[s][0] = ld_coh<CG>(b + (pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0));
 			} else {
 				T al[V];
-				ldc<V>(b + j0, al);
+				ldc<V, CG>(b + j0, al);
 				if (pull_dj(s) == 0) {
 #pragma unroll
 					for (int k = 0; k < V; k++) f[s][k] = al[k];
 				} else if (pull_dj(s) < 0) {
-					f[s][0] = b[jl];
+					f[s][0] = ld_coh<CG>(b + jl);
 #pragma unroll
 					for (int k = 1; k < V; k++) f[s][k] = al[k - 1];
 				} else {
-					f[s][V - 1] = b[jr];
+					f[s][V - 1] = ld_coh<CG>(b + jr);
 #pragma unroll
 					for (int k = 0; k < V - 1; k++) f[s][k] = al[k + 1];
 				}
@@ -817,6 +823,127 @@ stream_collide_persistent_kernel(const __grid_constant__ StepParams<T> p, const 
 			st_release_gpu(q.progress + blockIdx.x, t + 1);
 		}
 		const T *tmp = src; src = dst; dst = const_cast<T *>(tmp);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Dataflow form of the temporally blocked in-place engine (single slab, full-width row bands): ONE launch runs a
+// whole macro-step, i.e. every (row piece, level) of the wavefront schedule.  The list of those "launches" is cut
+// into items of one row x one column chunk; CTA b takes items b, b + gridDim.x, ... in list order.  What the
+// kernel boundary between two levels used to guarantee is checked per item instead: (level s, row r) starts when
+// rows r-1, r, r+1 (periodic) have finished level s-1 -- the only dependency the in-place kernels have (read
+// after write; see the temporal blocking notes in lbm_api.cu) -- read from per-(level,row) counters of finished
+// chunks.  The list order is a topological order (tests/test_tb_schedule.py) and all CTAs are co-resident
+// (cooperative launch), so the lowest unfinished item can always run: no deadlock.  No drain / refill between
+// the ~60 short launches of a macro-step; the small inverted-pyramid levels hide between the big ones.
+// Level 0 depends on the previous macro-step only, i.e. on the previous launch.
+// ---------------------------------------------------------------------------
+struct DfLaunch {
+	int level, r0, rows, tail_source;
+	unsigned first;             // index of this launch's first item
+};
+struct DfParams {
+	const DfLaunch *list;
+	int nlaunch;
+	unsigned nitems;
+	int chunks;                 // column chunks per row
+	int iters;                  // vectors per thread and item; a chunk is blockDim.x * iters vectors
+	int *cnt;                   // [levels][nxl] finished chunks, zeroed before the launch
+	int *abort;                 // set when a wait timed out
+	int levels;
+	unsigned long long timeout_ns;
+};
+
+// Both phases in one kernel: left alone ptxas spends 88 registers on the vec-1 DP instance (the phase kernels take 56-59,
+// and the L2-resident DP kernel loses 15 % at 104, profiles/r01_run25/NOTE.md) -- capped at 64 like the SP kernels.
+#ifndef LBM_DF_MINB
+#define LBM_DF_MINB 8
+#endif
+struct DfItem { int level, r, tail_source; unsigned ch; };
+
+__device__ __forceinline__ DfItem df_locate(const DfParams &q, unsigned n, int &cur, int nxl)
+{
+	while (cur + 1 < q.nlaunch && n >= q.list[cur + 1].first) cur++;
+	const DfLaunch L = q.list[cur];
+	const unsigned local = n - L.first;
+	const unsigned rr = local / (unsigned)q.chunks;
+	DfItem it;
+	it.level = L.level; it.tail_source = L.tail_source;
+	it.ch = local - rr * (unsigned)q.chunks;
+	it.r = L.r0 + (int)rr;
+	if (it.r >= nxl) it.r -= nxl;
+	return it;
+}
+// the counter thread `t` (0..2) of a CTA watches for an item: row r-1+t of the level below
+__device__ __forceinline__ const int *df_dep(const DfParams &q, const DfItem &it, int t, int nxl)
+{
+	int rd = it.r - 1 + t;
+	if (rd < 0) rd += nxl;
+	if (rd >= nxl) rd -= nxl;
+	return q.cnt + (size_t)(it.level - 1) * nxl + rd;
+}
+__device__ __forceinline__ void red_release_gpu_add(int *p, int v)
+{
+	asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <typename T, int V, bool CG>
+__global__ void __launch_bounds__(sizeof(T) == 4 ? 256 : 128, sizeof(T) == 4 ? 4 : LBM_DF_MINB)
+stream_collide_aa_dataflow_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ DfParams q)
+{
+	const uint32_t nvec = (uint32_t)p.ny / V;
+	__shared__ int s_abort;
+	if (threadIdx.x == 0) s_abort = 0;
+	const bool watcher = threadIdx.x < 3;
+	int cur = 0;
+	unsigned n = blockIdx.x;
+	if (n >= q.nitems) return;
+	DfItem it = df_locate(q, n, cur, p.nxl);
+	int seen = (watcher && it.level > 0) ? ld_acquire_gpu(df_dep(q, it, (int)threadIdx.x, p.nxl)) : q.chunks;
+	for (;;) {
+		if (watcher && it.level > 0 && seen < q.chunks) {        // usually already seen full one item ago (below)
+			const int *c = df_dep(q, it, (int)threadIdx.x, p.nxl);
+			unsigned long long t0 = 0;
+			uint32_t spins = 0;
+			while (ld_acquire_gpu(c) < q.chunks) {
+				if ((++spins & 255u) != 0) continue;
+				unsigned long long now;
+				asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+				if (t0 == 0) t0 = now;
+				if (now - t0 > q.timeout_ns || ld_acquire_gpu(q.abort)) { *q.abort = 1; s_abort = 1; break; }
+			}
+		}
+		__syncthreads();
+		if (s_abort) return;
+		// next item of this CTA: look at its counters now, the answer arrives while this item is computed
+		const unsigned nn = n + gridDim.x;
+		DfItem nit = it;
+		if (nn < q.nitems) {
+			nit = df_locate(q, nn, cur, p.nxl);
+			seen = (watcher && nit.level > 0) ? ld_acquire_gpu(df_dep(q, nit, (int)threadIdx.x, p.nxl)) : q.chunks;
+		}
+		const uint32_t v0 = it.ch * blockDim.x * (uint32_t)q.iters + threadIdx.x;
+		for (int u = 0; u < q.iters; u++) {
+			const uint32_t jv = v0 + (uint32_t)u * blockDim.x;
+			if (jv < nvec) {
+				const int j0 = (int)jv * V;
+				T f[9][V], o[9][V];
+				if (it.level & 1) {
+					aa_load<T, V, 2, CG>(p, it.r, j0, f);
+					relax_sites<T, V>(p, f, o, it.r, j0, it.tail_source);
+					aa_store<T, V, 2>(p, it.r, j0, o);
+				} else {
+					aa_load<T, V, 1, CG>(p, it.r, j0, f);
+					relax_sites<T, V>(p, f, o, it.r, j0, it.tail_source);
+					aa_store<T, V, 1>(p, it.r, j0, o);
+				}
+			}
+		}
+		__syncthreads();                                         // all of this item's stores issued ...
+		if (threadIdx.x == 0)                                    // ... and visible device-wide before the row's counter moves
+			red_release_gpu_add(q.cnt + (size_t)it.level * p.nxl + it.r, 1);
+		if (nn >= q.nitems) return;
+		n = nn; it = nit;
 	}
 }
 

@@ -208,16 +208,18 @@ def make_ring(nx, ny, nslabs, prec="dp", device=0, bounds=None, **kw):
     return slabs
 
 
-def tb_schedule(nx, ny, tb_depth, tb_rows=0, tb_cols=0, prec="dp", multi=False):
+def tb_schedule(nx, ny, tb_depth, tb_rows=0, tb_cols=0, prec="dp", multi=False, dataflow=False):
     """Launch list of one temporal-blocking macro-step (lbm_tb_schedule; host logic, no GPU):
     returns (depth_used, [(level, r0, r1, j0, j1), ...]); ranges past nx / ny wrap periodically,
     j0 == j1 == 0 means whole rows.  ``multi=True``: the list of one slab of a multi-slab ring, each entry
-    with a sixth field ``seam`` (bit 0: wait for the neighbours' previous event first, bit 1: announce after)."""
+    with a sixth field ``seam`` (bit 0: wait for the neighbours' previous event first, bit 1: announce after).
+    ``dataflow=True``: the order in which the dataflow kernel (``Tuning.dataflow``) takes a single slab's launches."""
     lib = _capi.load(prec)
     k = ctypes.c_int()
-    n = lib.dll.lbm_tb_schedule(nx, ny, int(multi), tb_depth, tb_rows, tb_cols, ctypes.byref(k), None, 0)
+    mode = 2 if dataflow else int(bool(multi))
+    n = lib.dll.lbm_tb_schedule(nx, ny, mode, tb_depth, tb_rows, tb_cols, ctypes.byref(k), None, 0)
     if n < 0:
         raise _capi.LbmError(_capi.ERR_ARG, lib.dll.lbm_last_error().decode())
     buf = (ctypes.c_int * (6 * max(n, 1)))()
-    lib.dll.lbm_tb_schedule(nx, ny, int(multi), tb_depth, tb_rows, tb_cols, ctypes.byref(k), buf, n)
-    return k.value, [tuple(buf[6 * i + m] for m in range(6 if multi else 5)) for i in range(n)]
+    lib.dll.lbm_tb_schedule(nx, ny, mode, tb_depth, tb_rows, tb_cols, ctypes.byref(k), buf, n)
+    return k.value, [tuple(buf[6 * i + m] for m in range(6 if mode == 1 else 5)) for i in range(n)]

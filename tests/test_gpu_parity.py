@@ -57,7 +57,10 @@ ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), 
            # 2-D tiles: column strips as well as row bands (falls back to bands where ny is not a multiple of 8)
            "inplace+tb2d": dict(inplace=1, tb_depth=4, tb_rows=16, tb_cols=256, graph=1, pdl=1),
            # phase 1 with aligned vector accesses only, +-1 column elements exchanged by warp shuffles
-           "inplace+shuffle": dict(inplace=1, neighbour=0), "inplace+shuffle+tb2d": dict(inplace=1, neighbour=0, vec=2, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1)}
+           "inplace+shuffle": dict(inplace=1, neighbour=0), "inplace+shuffle+tb2d": dict(inplace=1, neighbour=0, vec=2, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1),
+           # a whole macro-step of the wavefront schedule in ONE launch, per-row dependency counters instead of kernel boundaries
+           "inplace+dataflow": dict(inplace=1, tb_depth=8, tb_rows=12, tb_cols=1 << 20, vec=1, dataflow=1),
+           "inplace+dataflow+l1": dict(inplace=1, tb_depth=6, tb_cols=1 << 20, dataflow=3, hints=1, block=64)}
 
 
 def _split(engine_kw):
@@ -191,6 +194,25 @@ def test_every_kernel_variant_is_bit_identical(prec):
             lat.run(2)
             lat.run(c["steps"] - 2)
             _assert_same(lat.download("A"), o.f_view("A"), f"wavefront fA (2 + {c['steps'] - 2} steps) with {tune}")
+        # the same schedules through the dataflow kernel (one launch per macro-step)
+        for n, (k, h, u, extra) in enumerate(((2, 0, 1, {}), (4, 7, 1, dict(block=32)), (8, 16, 2, dict(ctas_per_sm=1)), (46, 3, 1, {}),
+                                              (10, 200, 5, dict(hints=1)), (4, 1, 1, dict(block=64, ctas_per_sm=2)), (6, 90, 64, {}),
+                                              (16, 40, 3, dict(block=256, hints=1)))):
+            tune = dict(dict(vec=vecs[n % len(vecs)], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=1, graph=0,
+                             tb_depth=k, tb_rows=h, tb_cols=1 << 20, dataflow=u), **extra)
+            lat.set_tuning(**tune)
+            lat.upload(fA, walls)
+            l0 = lat.launches
+            lat.run(c["steps"])
+            _assert_same(lat.download("A"), o.f_view("A"), f"dataflow fA with {tune}")
+            if c["ny"] % (8 if prec == "sp" else 4) == 0 and 2 * k + 2 <= c["nx"]:
+                # prologue (2) + one launch per macro-step: (steps - k) // k full ones, then the last one or two
+                assert lat.launches - l0 <= 2 + -(-c["steps"] // k) + 1, "the dataflow kernel did not run"
+            lat.upload(fA, walls)
+            lat.run(2)
+            lat.run(c["steps"] - 2)
+            _assert_same(lat.download("A"), o.f_view("A"), f"dataflow fA (2 + {c['steps'] - 2} steps) with {tune}")
+        lat.set_tuning(dataflow=0, hints=0)
 
 
 @pytest.mark.parametrize("prec", ["dp", "sp"])
