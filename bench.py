@@ -454,7 +454,7 @@ def bench_multi(args):
                            "parallelism": f"row slabs x{world}, halo rows stored peer-to-peer over NVLink ({args.transport}), boundary rows on a second stream",
                            "engine": ("in-place single buffer per slab (AA kernels) + 2-D temporal blocking in L2 across the slab seams (library defaults)"
                                       if args.engine == "inplace" else "A/B double buffer per slab, one pull kernel per timestep (HBM-bound)"),
-                           "l2": ("tens of GB per GPU, far larger than L2; the in-place engine keeps ~60 MB tiles L2-resident for 16 (DP) / 8 (SP) timesteps, "
+                           "l2": ("tens of GB per GPU, far larger than L2; the in-place engine keeps ~60 MB tiles L2-resident for 16 timesteps, "
                                   "so algorithmic GB/s may exceed the HBM peak (roofline.frac > 1); nothing is flushed because that residency is the engine"
                                   if args.engine == "inplace" else "tens of GB per GPU, far larger than L2: every timestep streams the slab through HBM")},
                 "roofline": dp["roofline"], "e2e": dp["e2e"], "gpu_launches": dp["launches"], "clocks": clocks,

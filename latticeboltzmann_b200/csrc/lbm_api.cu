@@ -259,7 +259,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		 * thousands of kernel nodes from a graph measured 5-10 % slower).  DP 8192x32768: 62.1 vs 47.8 GLUPS. */
 		c->tune.pdl = 1;
 		c->tune.graph = 0;
-		c->tune.tb_depth = sizeof(real_t) == 8 ? 16 : 8;
+		c->tune.tb_depth = 16;                                   /* SP since its kernels run at 64 registers: 104.4 (k 16) vs 102.1 (k 8), r01_run28 */
 		c->tune.vec = sizeof(real_t) == 8 ? 1 : 4;
 	}
 	if (c->inplace && (unsigned long long)c->nxl * c->ny <= (16ull << 20)) {
@@ -269,12 +269,11 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		c->tune.pdl = 1;
 		c->tune.graph = 10;
 		const double row_bytes = 9.0 * c->ldy * sizeof(real_t);
-		const int k = sizeof(real_t) == 8 ? 16 : 8;
+		const int k = 16;
 		const double band = sizeof(real_t) == 8 ? 45e6 : 60e6;
-		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) {
-			c->tune.tb_depth = k;
-			if (sizeof(real_t) == 4) c->tune.vec = 2;                /* SP 800x4000: 98.7 (vec 2) vs 83.8 GLUPS (vec 4), profiles/r01_run11 */
-		}
+		/* SP: vec 4 and k = 16 since the SP kernels run at 64 registers -- 800x4000 105.7 GLUPS against 98.7 for the
+		 * earlier vec 2 / k = 8, 1600x4000 109.9 against 101.9 (profiles/r01_run28) */
+		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) c->tune.tb_depth = k;
 	}
 	*out = c;
 	return LBM_OK;
