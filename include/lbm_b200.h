@@ -199,6 +199,11 @@ typedef struct {
 	                     item of level s starts when rows i-1, i, i+1 have finished level s-1 (per-row counters), which is
 	                     all the kernel boundaries guaranteed.  No drain/refill between the short launches.  With it,
 	                     hints = 1 selects L1-cached loads (default: ld.global.cg).  0 = off */
+	int fuse_rows;    /* in-place single-slab contexts: >= 3 = steps 2,3 | 4,5 | ... of a run are taken in pairs by ONE kernel
+	                     (phase 2 of a step and phase 1 of the next): CTAs own tiles of fuse_rows rows x block (64 or 128)
+	                     columns and pass the intermediate populations through shared memory, so a site's nine values
+	                     are loaded and stored once per TWO timesteps; the rims of the tiles take their phase 1 in a
+	                     second, small kernel.  0 = off */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);

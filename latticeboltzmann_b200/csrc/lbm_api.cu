@@ -713,6 +713,61 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 	return LBM_OK;
 }
 
+/* ---- fused pairs: phase 2 of step t and phase 1 of step t+1 in one pass (lbm_tuning.fuse_rows) ---- */
+template <typename K, typename A, typename B>
+cudaError_t launch_kernel2(K kern, const A &a, const B &b, dim3 grid, unsigned block, cudaStream_t st, int pdl)
+{
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+	cudaLaunchAttribute at[1];
+	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	at[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+	return cudaLaunchKernelEx(&cfg, kern, a, b);
+}
+
+bool pairs_ok(const lbm_ctx *c)
+{
+	return c->inplace && c->sync_mode == SYNC_SELF && c->tune.fuse_rows >= 3 && c->vw > 1 && c->nyvec == c->ny;
+}
+
+/* rows [r0, r1): phase 2 (tail1) of every site + phase 1 (tail2) of the tile interiors, then phase 1 of the tile rims */
+int launch_pair(lbm_ctx *c, int r0, int r1, int tail1, int tail2, cudaStream_t st)
+{
+	StepParams<real_t> p = make_params(c, 1, r0, r1, tail1);
+	const int tr = c->tune.fuse_rows;
+	const int tc = c->tune.block == 64 ? 64 : 128;
+	PairParams q;
+	q.tile_rows = tr; q.tail_source2 = tail2;
+	const unsigned row_tiles = (unsigned)((r1 - r0 + tr - 1) / tr), col_tiles = (unsigned)((c->ny + tc - 1) / tc);
+	if (row_tiles > 65535u) return fail(LBM_ERR_ARG, "fuse_rows %d: %u row tiles", tr, row_tiles);
+	cudaError_t e = tc == 64 ? launch_kernel2(stream_collide_aa_pair_kernel<real_t, 64>, p, q, dim3(col_tiles, row_tiles), 64, st, c->tune.pdl)
+	                         : launch_kernel2(stream_collide_aa_pair_kernel<real_t, 128>, p, q, dim3(col_tiles, row_tiles), 128, st, c->tune.pdl);
+	if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_aa_pair_kernel: %s", cudaGetErrorString(e));
+	StepParams<real_t> pe = make_params(c, 0, r0, r1, tail2);
+	EdgeParams qe;
+	qe.tile_rows = tr; qe.tile_cols = tc; qe.edge_rows = 2 * (int)row_tiles; qe.col_tiles = (int)col_tiles;
+	const unsigned gy = (unsigned)qe.edge_rows + (unsigned)(r1 - r0);
+	if (gy > 65535u) return fail(LBM_ERR_ARG, "fuse_rows %d: %u edge launch rows", tr, gy);
+	const unsigned need = (unsigned)c->ny > 2 * col_tiles ? (unsigned)c->ny : 2 * col_tiles;
+	e = launch_kernel2(stream_collide_aa_edges_kernel<real_t>, pe, qe, dim3((need + 127) / 128, gy), 128, st, c->tune.pdl);
+	if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_aa_edges_kernel: %s", cudaGetErrorString(e));
+	c->launches += 2;
+	return LBM_OK;
+}
+
+/* nsteps (even) as: phase 1 | (phase 2 + phase 1) x (nsteps/2 - 1) | phase 2 */
+int run_pairs(lbm_ctx *c, int nsteps)
+{
+	int rc;
+	struct Scope { lbm_ctx *c; Scope(lbm_ctx *c_) : c(c_) { c->in_wavefront = 1; } ~Scope() { c->in_wavefront = 0; } } scope(c);
+	cudaStream_t st = c->stream[0];
+	if ((rc = launch_step(c, 0, 0, c->nxl, 1, st))) return rc;
+	for (int t = 1; t + 1 < nsteps; t += 2)
+		if ((rc = launch_pair(c, 0, c->nxl, 1, 1, st))) return rc;
+	return launch_step(c, 1, 0, c->nxl, 0, st);
+}
+
 /* ---- dataflow kernel: a whole macro-step in one launch (single slab, whole-row pieces) ---- */
 /* Its item order: tb_for_each_launch's, except that inverted-pyramid level s is issued right after level s-1 of the
  * last other row piece instead of after all of that piece's levels.  Valid: inverted level s reads rows
@@ -1066,6 +1121,7 @@ int lbm_run(lbm_ctx *c, int nsteps)
 	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
 	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
 	if (use_persistent(c)) return launch_persistent(c, LBM_BUF_A, nsteps, 0, c->stream[0]);
+	if (pairs_ok(c)) return run_pairs(c, nsteps);
 	if (c->inplace && (c->sync_mode == SYNC_SELF || c->sync_mode == SYNC_FLAGS) && c->tune.tb_depth >= 2) return run_wavefront(c, nsteps);
 	int t = 0;
 	if (c->tune.graph > 0 && c->sync_mode == SYNC_SELF) {
@@ -1265,6 +1321,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.vec_phase1 != 0 && ((n.vec_phase1 != 1 && n.vec_phase1 != 2 && n.vec_phase1 != 4 && n.vec_phase1 != 8) || n.vec_phase1 > vmax))
 		return fail(LBM_ERR_ARG, "lbm_set_tuning: vec_phase1 %d", n.vec_phase1);
 	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
+	if (n.fuse_rows < 0 || (n.fuse_rows > 0 && n.fuse_rows < 3) || n.fuse_rows > 4096) return fail(LBM_ERR_ARG, "lbm_set_tuning: fuse_rows %d (0 or 3..4096)", n.fuse_rows);
 	if (n.dataflow < 0 || n.dataflow > 64) return fail(LBM_ERR_ARG, "lbm_set_tuning: dataflow %d (0..64)", n.dataflow);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");

@@ -948,6 +948,129 @@ stream_collide_aa_dataflow_kernel(const __grid_constant__ StepParams<T> p, const
 }
 
 // ---------------------------------------------------------------------------
+// Fused pair: phase 2 of one step and phase 1 of the next in ONE pass over memory.
+//   Phase 2 is local (site x relaxes the nine slots of x), phase 1 of the following step pulls f_s from slot s of
+//   x + pull(s) -- i.e. the phase-2 result o_s of that neighbour.  A CTA owns a tile of `tile_rows` rows x TC
+//   columns, one thread per column, and walks the rows: at row r it runs phase 2 of (r, c), leaves the nine
+//   results in a ring of rows in shared memory, and then runs phase 1 of (r-1, c) from the ring.  For a site
+//   whose 3x3 neighbourhood lies inside the tile ("interior") the intermediate populations never travel: 9 loads
+//   and 9 stores for TWO timesteps, half the traffic of the two separate kernels (to L2 and, where the lattice
+//   does not fit it, to HBM).
+//   Sites on the rim of a tile ("edge": first/last row, first/last column) cannot take phase 1 here (a neighbour's
+//   phase-2 result belongs to another CTA); they store their phase-2 result the ordinary way and
+//   stream_collide_aa_edges_kernel gives them phase 1 afterwards.  That kernel reads slot k of interior sites next to
+//   the rim as well, so an interior site stores o_k into its slot k wherever the slot's consumer x - pull(k) is an
+//   edge site; every other slot of an interior site receives the phase-1 result of its interior consumer, exactly
+//   where the ordinary phase 1 puts it.  Each slot is written by one thread per sub-step and tiles read and write
+//   their own sites only: no ordering between CTAs is needed.  Same relax_sites() as everywhere: bit-identical.
+//   Rows 0 and nxl-1 of a slab must be tile edges (their halo traffic is the ordinary kernels' business).
+// ---------------------------------------------------------------------------
+struct PairParams {
+	int tile_rows;              // rows per tile (>= 3 for any interior)
+	int tail_source2;           // tail_source of the phase-1 half (StepParams.tail_source is the phase-2 half's)
+};
+
+#ifndef LBM_PAIR_MINB
+#define LBM_PAIR_MINB 0
+#endif
+template <typename T, int TC>
+__global__ void __launch_bounds__(TC, LBM_PAIR_MINB)
+stream_collide_aa_pair_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ PairParams q)
+{
+	asm volatile("griddepcontrol.launch_dependents;");
+	// four-row ring: row r is written while rows r-3..r-1 may still be read, so one barrier per row is enough (a thread
+	// reaches the write of row r+2, which reuses the slot of r-2, only past the barrier of row r+1, i.e. after every
+	// thread has finished reading for row r)
+	__shared__ T sh[4][9][TC];
+	const int j = (int)threadIdx.x;
+	const int c0 = (int)blockIdx.x * TC;
+	const int c1 = min(c0 + TC, p.ny);
+	const int c = c0 + j;
+	const bool live = c < c1;
+	const bool col_edge = c == c0 || c == c1 - 1;
+	const int tr0 = p.r0 + (int)blockIdx.y * q.tile_rows;
+	const int tr1 = min(tr0 + q.tile_rows, p.r1);
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	// the nine populations of row r are loaded one row ahead (nothing writes a row of this tile before its own phase 2
+	// has read it: phase 1 of row r-1 reaches rows r-2..r only, and other CTAs never write this tile's sites)
+	T fn[9][1];
+	if (live) aa_load<T, 1, 2>(p, tr0, c, fn);
+	int cur = 0;                                             // ring slot of row r; row r-1 in (cur+3)&3, row r-2 in (cur+2)&3
+	for (int r = tr0; r < tr1; r++) {
+		if (live) {
+			T f[9][1], o[9][1];
+#pragma unroll
+			for (int s = 0; s < 9; s++) f[s][0] = fn[s][0];
+			if (r + 1 < tr1) aa_load<T, 1, 2>(p, r + 1, c, fn);
+			relax_sites<T, 1>(p, f, o, r, c, p.tail_source);
+#pragma unroll
+			for (int s = 0; s < 9; s++) sh[cur][s][j] = o[s][0];
+			if (col_edge || r == tr0 || r == tr1 - 1) {
+				aa_store<T, 1, 2>(p, r, c, o);
+			} else {
+				T *const own = p.dst + (size_t)(r + 1) * p.ldy + c;
+				const bool dn = r - 1 == tr0, up = r + 1 == tr1 - 1, lf = c - 1 == c0, rt = c + 1 == c1 - 1;
+#pragma unroll
+				for (int k = 1; k < 9; k++) {                    // consumer of slot k: site (r - pull_di(k), c - pull_dj(k))
+					const bool row_hit = pull_di(k) > 0 ? dn : pull_di(k) < 0 ? up : false;
+					const bool col_hit = pull_dj(k) > 0 ? lf : pull_dj(k) < 0 ? rt : false;
+					if (row_hit || col_hit) own[(size_t)k * p.plane] = o[k][0];
+				}
+			}
+		}
+		__syncthreads();
+		if (live && !col_edge && r - 1 > tr0) {                  // phase 1 of (r-1, c): rows r-2, r-1, r are in the ring
+			const int slot_of[3] = {(cur + 2) & 3, (cur + 3) & 3, cur};
+			T f[9][1], o[9][1];
+#pragma unroll
+			for (int s = 0; s < 9; s++) f[s][0] = sh[slot_of[pull_di(s) + 1]][s][j + pull_dj(s)];
+			relax_sites<T, 1>(p, f, o, r - 1, c, q.tail_source2);
+			aa_store<T, 1, 1>(p, r - 1, c, o);
+		}
+		cur = (cur + 1) & 3;
+	}
+}
+
+// phase 1 for the sites the pair kernel left out: the first and last row of every row tile (whole rows), and the first
+// and last column of every column tile in the other rows.  blockIdx.y < edge_rows: row ordinal; beyond: rows of the
+// launch's range, threads over the column-tile rims.
+struct EdgeParams {
+	int tile_rows, tile_cols;
+	int edge_rows;              // 2 per row tile
+	int col_tiles;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128)
+stream_collide_aa_edges_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ EdgeParams q)
+{
+	asm volatile("griddepcontrol.launch_dependents;");
+	int r, c;
+	if ((int)blockIdx.y < q.edge_rows) {
+		const int t = (int)blockIdx.y >> 1;
+		const int tr0 = p.r0 + t * q.tile_rows, tr1 = min(tr0 + q.tile_rows, p.r1);
+		r = (blockIdx.y & 1) ? tr1 - 1 : tr0;
+		if ((blockIdx.y & 1) && tr1 - 1 == tr0) return;          // one-row tile: once
+		c = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+		if (c >= p.ny) return;
+	} else {
+		r = p.r0 + (int)blockIdx.y - q.edge_rows;
+		const int rel = (r - p.r0) % q.tile_rows;
+		if (rel == 0 || rel == q.tile_rows - 1 || r == p.r1 - 1) return;     // a tile's first / last row: done above
+		const int e = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+		if (e >= 2 * q.col_tiles) return;
+		const int c0 = (e >> 1) * q.tile_cols, c1 = min(c0 + q.tile_cols, p.ny);
+		c = (e & 1) ? c1 - 1 : c0;
+		if ((e & 1) && c1 - 1 == c0) return;
+	}
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	T f[9][1], o[9][1];
+	aa_load<T, 1, 1>(p, r, c, f);
+	relax_sites<T, 1>(p, f, o, r, c, p.tail_source);
+	aa_store<T, 1, 1>(p, r, c, o);
+}
+
+// ---------------------------------------------------------------------------
 // scalar-order kernel: StreamCollide (LB.c:216-302) for columns [jmin,jmax) --
 // the ragged tail j >= NYVECMAX of a vector build, or everything when the
 // matched reference build is a prec_*_serial.h one.  One site per thread.

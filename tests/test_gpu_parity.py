@@ -60,7 +60,9 @@ ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), 
            "inplace+shuffle": dict(inplace=1, neighbour=0), "inplace+shuffle+tb2d": dict(inplace=1, neighbour=0, vec=2, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1),
            # a whole macro-step of the wavefront schedule in ONE launch, per-row dependency counters instead of kernel boundaries
            "inplace+dataflow": dict(inplace=1, tb_depth=8, tb_rows=12, tb_cols=1 << 20, vec=1, dataflow=1),
-           "inplace+dataflow+l1": dict(inplace=1, tb_depth=6, tb_cols=1 << 20, dataflow=3, hints=1, block=64)}
+           "inplace+dataflow+l1": dict(inplace=1, tb_depth=6, tb_cols=1 << 20, dataflow=3, hints=1, block=64),
+           # phase 2 of a step and phase 1 of the next fused in one kernel (tiles of fuse_rows x block sites, shared memory)
+           "inplace+pairs": dict(inplace=1, fuse_rows=5, pdl=1), "inplace+pairs64": dict(inplace=1, fuse_rows=9, block=64, tb_depth=0)}
 
 
 def _split(engine_kw):
@@ -213,6 +215,21 @@ def test_every_kernel_variant_is_bit_identical(prec):
             lat.run(c["steps"] - 2)
             _assert_same(lat.download("A"), o.f_view("A"), f"dataflow fA (2 + {c['steps'] - 2} steps) with {tune}")
         lat.set_tuning(dataflow=0, hints=0)
+        # fused pairs (phase 2 + next phase 1 in one kernel, rims in a second): tile heights around the edge cases
+        for tr, blk, pdl in ((3, 128, 0), (4, 64, 1), (7, 128, 1), (16, 64, 0), (95, 128, 1), (96, 64, 0), (200, 128, 0), (4096, 64, 1)):
+            tune = dict(vec=1, neighbour=1, hints=0, block=blk, ctas_per_sm=0, persistent=0, pdl=pdl, graph=0, tb_depth=0, fuse_rows=tr)
+            lat.set_tuning(**tune)
+            lat.upload(fA, walls)
+            l0 = lat.launches
+            lat.run(c["steps"])
+            _assert_same(lat.download("A"), o.f_view("A"), f"fused pairs fA with {tune}")
+            if c["ny"] % (8 if prec == "sp" else 4) == 0:
+                assert lat.launches - l0 == 2 + 2 + 2 * (c["steps"] // 2 - 1), "the pair kernel did not run"
+            lat.upload(fA, walls)
+            lat.run(2)
+            lat.run(c["steps"] - 2)
+            _assert_same(lat.download("A"), o.f_view("A"), f"fused pairs fA (2 + {c['steps'] - 2} steps) with {tune}")
+        lat.set_tuning(fuse_rows=0)
 
 
 @pytest.mark.parametrize("prec", ["dp", "sp"])
