@@ -46,7 +46,8 @@ def _structs(real):
                     ("hints", ctypes.c_int), ("ctas_per_sm", ctypes.c_int), ("persistent", ctypes.c_int),
                     ("pdl", ctypes.c_int), ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int),
                     ("tb_cols", ctypes.c_int), ("vec_phase1", ctypes.c_int), ("rows_per_thread", ctypes.c_int),
-                    ("dataflow", ctypes.c_int), ("fuse_rows", ctypes.c_int)]
+                    ("dataflow", ctypes.c_int), ("fuse_rows", ctypes.c_int),
+                    ("stage_smem", ctypes.c_int)]
 
     return Config, Scene, SlabInfo, Tuning
 

@@ -313,10 +313,10 @@ namespace {
 
 typedef void (*step_kernel_t)(const StepParams<real_t>);
 
-cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl, size_t smem = 0)
 {
 	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+	cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
 	cudaLaunchAttribute at[1];
 	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 	at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -407,6 +407,13 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			}
 			if (gy > 65535u) gy = 65535u;
 			const dim3 g2(gx, gy);
+			if (pipe == 1 && V == 1 && c->tune.stage_smem) {         /* next row staged in shared memory by cp.async (experimental) */
+				const unsigned blk = block > 256 ? 256 : block;
+				const dim3 g3((ncols + blk - 1) / blk, gy);
+				const size_t smem = (size_t)2 * 9 * blk * sizeof(real_t);
+				e = phase == 1 ? launch_kernel(stream_collide_aa_staged_kernel<real_t, 1>, p, g3, blk, st, pdl, smem)
+				               : launch_kernel(stream_collide_aa_staged_kernel<real_t, 2>, p, g3, blk, st, pdl, smem);
+			} else
 			switch (V) {
 			case 1: e = launch_aa_v<1>(phase, pipe, p, g2, block, st, pdl); break;
 			case 2: e = launch_aa_v<2>(phase, pipe, p, g2, block, st, pdl); break;
@@ -1322,6 +1329,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 		return fail(LBM_ERR_ARG, "lbm_set_tuning: vec_phase1 %d", n.vec_phase1);
 	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
 	if (n.fuse_rows < 0 || (n.fuse_rows > 0 && n.fuse_rows < 3) || n.fuse_rows > 4096) return fail(LBM_ERR_ARG, "lbm_set_tuning: fuse_rows %d (0 or 3..4096)", n.fuse_rows);
+	if (n.stage_smem < 0 || n.stage_smem > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: stage_smem %d", n.stage_smem);
 	if (n.dataflow < 0 || n.dataflow > 64) return fail(LBM_ERR_ARG, "lbm_set_tuning: dataflow %d (0..64)", n.dataflow);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");

@@ -730,6 +730,78 @@ stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 }
 
 // ---------------------------------------------------------------------------
+// In-place step, one site per thread, threads walking rows blockIdx.y, +gridDim.y, ... like PIPE == 1 -- but the nine
+// populations of the NEXT row travel global -> shared memory with cp.async (LDGSTS, 4 or 8 bytes per copy, each thread
+// its own nine) while the current row is relaxed, instead of into a second register set: the L2 latency is covered
+// without the registers that cost PIPE == 1 its occupancy, and without the serial load -> arithmetic -> store of a
+// looping thread (capped grids, DESIGN.md "What did NOT help" (2), (8)).  No barrier: a thread reads only what it copied
+// itself (cp.async.wait_group).  Safe in place for the reason PIPE == 1 is: a site's nine slots are its own.
+// Dynamic shared memory: 2 x 9 x blockDim.x elements.
+// STATUS: written after the round-1 GPU budget was spent; compiles (SASS: LDGSTS), not yet run on a GPU.  Off unless
+// lbm_tuning.stage_smem is set; its GPU test is gated by LBM_TEST_EXPERIMENTAL=1.
+// ---------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ void cp_async_elem(T *smem_dst, const T *gsrc)
+{
+	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gsrc), "n"(sizeof(T)) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// same addresses as aa_load<T, 1, PHASE>; dst = this thread's element of stage slot s, slots `stride` elements apart
+template <typename T, int PHASE>
+__device__ __forceinline__ void aa_stage_issue(const StepParams<T> &p, int r, int j0, T *dst, uint32_t stride)
+{
+	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;
+	if constexpr (PHASE == 2) {
+#pragma unroll
+		for (int s = 0; s < 9; s++) cp_async_elem<T>(dst + s * stride, own + (size_t)opposite(s) * p.plane + j0);
+	} else {
+		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
+		const int jr = j0 + 1 == p.ny ? 0 : j0 + 1;
+		const T *lrow[3] = {own - p.ldy, own, own + p.ldy};
+#pragma unroll
+		for (int s = 0; s < 9; s++)
+			cp_async_elem<T>(dst + s * stride, lrow[pull_di(s) + 1] + (size_t)s * p.plane + (pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0));
+	}
+}
+
+template <typename T, int PHASE>
+__global__ void __launch_bounds__(256)
+stream_collide_aa_staged_kernel(const __grid_constant__ StepParams<T> p)
+{
+	extern __shared__ __align__(16) unsigned char aa_stage_raw[];
+	T *const stage = reinterpret_cast<T *>(aa_stage_raw);        // [2][9][blockDim.x]
+	asm volatile("griddepcontrol.launch_dependents;");
+	const uint32_t ncol = (uint32_t)(p.jmax - p.jmin);
+	const uint32_t rows = (uint32_t)(p.r1 - p.r0);
+	const uint32_t jv = blockIdx.x * blockDim.x + threadIdx.x;
+	int j0 = p.jmin + (int)jv;
+	if (j0 >= p.ny) j0 -= p.ny;
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	uint32_t rr = blockIdx.y;
+	if (jv >= ncol || rr >= rows) return;
+	const uint32_t st = gridDim.y, bd = blockDim.x;
+	T *const mine = stage + threadIdx.x;
+	aa_stage_issue<T, PHASE>(p, aa_row(p, rr), j0, mine, bd);
+	cp_async_commit();
+	uint32_t b = 0;
+#pragma unroll 1
+	for (; rr < rows; rr += st) {
+		const int r = aa_row(p, rr);
+		if (rr + st < rows) aa_stage_issue<T, PHASE>(p, aa_row(p, rr + st), j0, mine + (b ^ 1u) * 9u * bd, bd);
+		cp_async_commit();                                       // (possibly empty) so that "all but the newest group" is this row's
+		cp_async_wait<1>();
+		T f[9][1], o[9][1];
+#pragma unroll
+		for (int s = 0; s < 9; s++) f[s][0] = mine[(b * 9u + (uint32_t)s) * bd];
+		relax_sites<T, 1>(p, f, o, r, j0, p.tail_source);
+		aa_store<T, 1, PHASE>(p, r, j0, o);
+		b ^= 1u;
+	}
+}
+
+// ---------------------------------------------------------------------------
 // Persistent multi-step kernel for lattices whose step is short (tens of microseconds): ONE
 // cooperative launch runs `nsteps` lattice steps.  Each CTA owns a fixed contiguous range of the
 // flattened (row, vector) space; instead of a grid-wide barrier per step, a CTA starts step t as
