@@ -205,7 +205,8 @@ typedef struct {
 	                     are loaded and stored once per TWO timesteps; the rims of the tiles take their phase 1 in a
 	                     second, small kernel.  0 = off */
 	int stage_smem;   /* EXPERIMENTAL (compiled, not yet run on a GPU): with rows_per_thread >= 2 and vec 1, the next row's
-	                     populations are staged in shared memory by cp.async instead of a second register set.  0 = off */
+	                     populations are staged in shared memory by cp.async instead of a second register set; 2 = phase 2
+	                     moves its row segments with TMA bulk copies (cp.async.bulk + mbarrier) both ways.  0 = off */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);

@@ -411,6 +411,11 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 				const unsigned blk = block > 256 ? 256 : block;
 				const dim3 g3((ncols + blk - 1) / blk, gy);
 				const size_t smem = (size_t)2 * 9 * blk * sizeof(real_t);
+				if (phase == 2 && c->tune.stage_smem == 2 && jc1 <= jc0) {   /* TMA bulk copies both ways; whole rows only */
+					const unsigned b2 = blk > 128 ? 128 : blk;
+					const dim3 g4(((unsigned)c->ny + b2 - 1) / b2, gy);
+					e = launch_kernel(stream_collide_aa_bulk2_kernel<real_t>, p, g4, b2, st, pdl, (size_t)4 * 9 * b2 * sizeof(real_t) + 16);
+				} else
 				e = phase == 1 ? launch_kernel(stream_collide_aa_staged_kernel<real_t, 1>, p, g3, blk, st, pdl, smem)
 				               : launch_kernel(stream_collide_aa_staged_kernel<real_t, 2>, p, g3, blk, st, pdl, smem);
 			} else
@@ -1329,7 +1334,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 		return fail(LBM_ERR_ARG, "lbm_set_tuning: vec_phase1 %d", n.vec_phase1);
 	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
 	if (n.fuse_rows < 0 || (n.fuse_rows > 0 && n.fuse_rows < 3) || n.fuse_rows > 4096) return fail(LBM_ERR_ARG, "lbm_set_tuning: fuse_rows %d (0 or 3..4096)", n.fuse_rows);
-	if (n.stage_smem < 0 || n.stage_smem > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: stage_smem %d", n.stage_smem);
+	if (n.stage_smem < 0 || n.stage_smem > 2) return fail(LBM_ERR_ARG, "lbm_set_tuning: stage_smem %d", n.stage_smem);
 	if (n.dataflow < 0 || n.dataflow > 64) return fail(LBM_ERR_ARG, "lbm_set_tuning: dataflow %d (0..64)", n.dataflow);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");

@@ -242,7 +242,10 @@ def test_staged_kernel_is_bit_identical(prec):
     o = _oracle(c, fA, walls, c["steps"])
     with _lattice(c, inplace=True) as lat:
         for rpt, extra in ((2, {}), (5, dict(tb_depth=4, tb_rows=9)), (3, dict(pdl=1, graph=2)), (96, {}), (7, dict(ctas_per_sm=1, block=64)),
-                           (4, dict(block=256)), (2, dict(tb_depth=4, tb_rows=20, tb_cols=128, pdl=1)), (1000, dict(block=32))):
+                           (4, dict(block=256)), (2, dict(tb_depth=4, tb_rows=20, tb_cols=128, pdl=1)), (1000, dict(block=32)),
+                           # 2: phase 2 through TMA bulk copies (whole rows), phase 1 through cp.async
+                           (2, dict(stage_smem=2)), (3, dict(stage_smem=2, tb_depth=4, tb_rows=9, pdl=1)), (96, dict(stage_smem=2, block=64)),
+                           (7, dict(stage_smem=2, block=32, pdl=1, graph=2)), (4, dict(stage_smem=2, tb_depth=4, tb_rows=20, tb_cols=128))):
             tune = dict(dict(vec=1, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0,
                              rows_per_thread=rpt, stage_smem=1), **extra)
             lat.set_tuning(**tune)

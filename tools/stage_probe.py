@@ -26,14 +26,14 @@ for prec, nx, ny, T in (("dp", 400, 2000, 4000), ("dp", 400, 4000, 2000), ("sp",
         rec = dict(prec=prec, nx=nx, ny=ny, engine="default", tb_depth=d["tb_depth"], vec=d["vec"], mlups=round(nx * ny * T / ms / 1e3, 1))
         out.append(rec); print(json.dumps(rec), flush=True)
         init(); lat.run(32); want = lat.download("A")
-        for blk in (128, 64, 256):
+        for mode, blk in ((1, 128), (1, 64), (1, 256), (2, 128), (2, 64)):     # 1: cp.async both phases; 2: TMA bulk copies in phase 2
             for rpt in (2, 3, 4, 6, 8, 16):
-                lat.set_tuning(vec=1, rows_per_thread=rpt, stage_smem=1, block=blk)
+                lat.set_tuning(vec=1, rows_per_thread=rpt, stage_smem=mode, block=blk)
                 init(); lat.run(32)
                 same = bool(np.array_equal(lat.download("A").view(np.uint8), want.view(np.uint8)))
                 lat.run_timed(min(T, 400))
                 ms = min(lat.run_timed(T) for _ in range(3))
-                rec = dict(prec=prec, nx=nx, ny=ny, engine="staged", rows_per_thread=rpt, block=blk, bit_identical=same,
+                rec = dict(prec=prec, nx=nx, ny=ny, engine="staged", stage_smem=mode, rows_per_thread=rpt, block=blk, bit_identical=same,
                            mlups=round(nx * ny * T / ms / 1e3, 1))
                 out.append(rec); print(json.dumps(rec), flush=True)
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
