@@ -200,3 +200,56 @@ def test_dataflow_execution_model(nx, ny, depth, rows, chunks, ctas):
         nxt[g] += len(nxt)
         left -= 1
     assert (level == k).all() and (cnt == chunks).all()
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE.json's full sizes: the 2-D site model above would need gigabytes, but the schedule is a product of two
+# 1-D schedules (column pieces outermost, row pieces next, levels innermost), so it is enough that (i) the launch
+# list really is that product and (ii) each axis' own piece order respects the 1-D dependencies (reach 1).
+# ---------------------------------------------------------------------------------------------------
+def _axis_check(n, k, pieces):
+    """pieces: list over axis pieces (in schedule order) of {level: (lo, hi)}; 1-D level model with reach 1"""
+    level = np.zeros(n, dtype=np.int16)
+    for ranges in pieces:
+        for s in range(k):
+            if s not in ranges:
+                continue
+            lo, hi = ranges[s]
+            idx = np.arange(lo, hi) % n
+            assert (level[idx] == s).all()
+            assert (level[(idx - 1) % n] >= s).all() and (level[(idx + 1) % n] >= s).all()
+            level[idx] = s + 1
+    assert (level == k).all()
+
+
+@pytest.mark.parametrize("nx,ny,depth,prec", [(8192, 32768, 16, "dp"), (8192, 32768, 16, "sp"), (16384, 65536, 16, "dp"),
+                                              (16384, 65536, 24, "dp"), (400, 4000, 16, "dp"), (800, 4000, 16, "sp")])
+def test_full_size_schedules_are_valid_products(nx, ny, depth, prec):
+    k, launches = tb_schedule(nx, ny, depth, 0, 0, prec)
+    assert k == depth
+    whole_rows = all(j0 == j1 == 0 for _, _, _, j0, j1 in launches)
+    # (column piece, row piece) groups: inside one the level rises strictly; a new column piece starts where a group's
+    # column range disagrees with the current piece's at a level both have (inverted pyramids are empty at level 0)
+    groups = []
+    for s, r0, r1, j0, j1 in launches:
+        if not groups or s <= groups[-1]["last"]:
+            groups.append(dict(cols={}, rows={}, last=-1))
+        g = groups[-1]
+        g["cols"][s] = (0, ny) if whole_rows else (j0, j1)
+        g["rows"][s] = (r0, r1)
+        g["last"] = s
+    col_pieces, row_pieces_of = [], []
+    for g in groups:
+        if not col_pieces or any(col_pieces[-1].get(s, cr) != cr for s, cr in g["cols"].items()):
+            col_pieces.append({})
+            row_pieces_of.append([])
+        col_pieces[-1].update(g["cols"])
+        row_pieces_of[-1].append(g["rows"])
+    _axis_check(ny, k, col_pieces)
+    assert set(col_pieces[0]) == set(range(k))                     # the column pyramid (or the whole-row piece) exists at every level
+    for cp, rp in zip(col_pieces, row_pieces_of):                  # every column piece sweeps the same row pieces, at the levels it has
+        want = [{s: rng for s, rng in ref.items() if s in cp} for ref in row_pieces_of[0]]
+        assert rp == [w for w in want if w]
+    _axis_check(nx, k, row_pieces_of[0])
+    area = sum((r1 - r0) * ((j1 - j0) if j1 > j0 else ny) for _, r0, r1, j0, j1 in launches)
+    assert area == k * nx * ny
