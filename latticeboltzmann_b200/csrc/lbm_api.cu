@@ -76,6 +76,7 @@ struct lbm_ctx {
 	Peer up, dn;
 	int sync_mode;
 	int epoch;
+	unsigned long long wait_timeout_ns;   /* neighbour barrier: give up (and raise the ring's abort word) after this long */
 	void *ipc_opened[6];
 	int n_ipc_opened;
 	lbm_tuning tune;
@@ -242,6 +243,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	c->up.flags = c->dn.flags = c->flags;
 	c->up.nxl = c->dn.nxl = c->nxl;
 	c->sync_mode = SYNC_SELF;
+	c->wait_timeout_ns = 20ull * 1000 * 1000 * 1000;
 
 	/* measured best on B200 at every size (profiles/r01_run2): direct neighbour loads, 128-thread CTAs */
 	c->tune.vec = default_vec(c);
@@ -407,11 +409,11 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			}
 			if (gy > 65535u) gy = 65535u;
 			const dim3 g2(gx, gy);
-			if (pipe == 1 && V == 1 && c->tune.stage_smem) {         /* next row staged in shared memory by cp.async (experimental) */
+			if (pipe == 1 && V == 1 && c->tune.stage_smem && c->nyvec == c->ny) {   /* next row staged in shared memory by cp.async */
 				const unsigned blk = block > 256 ? 256 : block;
 				const dim3 g3((ncols + blk - 1) / blk, gy);
 				const size_t smem = (size_t)2 * 9 * blk * sizeof(real_t);
-				if (phase == 2 && c->tune.stage_smem == 2 && jc1 <= jc0) {   /* TMA bulk copies both ways; whole rows only */
+				if (phase == 2 && c->tune.stage_smem == 2 && jc1 <= jc0 && ((size_t)c->ny * sizeof(real_t)) % 16 == 0) {   /* TMA bulk copies both ways; whole rows of 16-byte units only */
 					const unsigned b2 = blk > 128 ? 128 : blk;
 					const dim3 g4(((unsigned)c->ny + b2 - 1) / b2, gy);
 					e = launch_kernel(stream_collide_aa_bulk2_kernel<real_t>, p, g4, b2, st, pdl, (size_t)4 * 9 * b2 * sizeof(real_t) + 16);
@@ -542,7 +544,7 @@ int launch_signal(lbm_ctx *c, cudaStream_t st)
 }
 int launch_wait(lbm_ctx *c, cudaStream_t st)
 {
-	flag_wait_kernel<<<1, 1, 0, st>>>(c->flags, c->epoch, 20ull * 1000 * 1000 * 1000);
+	flag_wait_kernel<<<1, 1, 0, st>>>(c->flags, c->up.flags + 3, c->dn.flags + 3, c->epoch, c->wait_timeout_ns);
 	CK(cudaGetLastError());
 	c->launches++;
 	return LBM_OK;
@@ -1294,13 +1296,13 @@ int lbm_print_lattice(lbm_ctx *c, const char *path)
 	if ((rc = lbm_macroscopic(c, nullptr, ux.data(), uy.data()))) return rc;
 	FILE *fp = fopen(path, "w");
 	if (!fp) return fail(LBM_ERR_IO, "Error opening file %s", path);       /* LB.c:616 */
-	std::vector<char> line((size_t)c->ny * 24 + 8);
+	std::vector<char> line((size_t)c->ny * 400 + 8);                       /* "%.10lf" of DBL_MAX is 320 characters (a diverged run) */
 	for (int i = 0; i < c->nxl; i++) {
 		size_t pos = 0;
 		for (int j = 0; j < c->ny; j++) {
 			const real_t a = ux[(size_t)i * c->ny + j], b = uy[(size_t)i * c->ny + j];
 			const real_t u2 = a * a + b * b;                                 /* LB.c:631, real_t arithmetic */
-			pos += (size_t)snprintf(&line[pos], 24, "%.10lf", (double)u2);   /* LB.c:633 */
+			pos += (size_t)snprintf(&line[pos], 398, "%.10lf", (double)u2);  /* LB.c:633 */
 			if (j < c->ny - 1) { line[pos++] = ','; line[pos++] = ' '; }     /* LB.c:634 */
 		}
 		line[pos++] = '\n';

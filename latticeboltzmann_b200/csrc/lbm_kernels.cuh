@@ -1478,15 +1478,22 @@ __global__ void flag_signal_kernel(volatile int *up_slot, volatile int *dn_slot,
 	__threadfence_system();
 }
 // wait: spin until both neighbours have announced `epoch`.  The spinners live on DIFFERENT
-// GPUs than the signallers.  Gives up after ~timeout_ns and raises flags[3].
-__global__ void flag_wait_kernel(volatile int *flags, int epoch, unsigned long long timeout_ns)
+// GPUs than the signallers.  flags[3] is the ring's abort word: a wait that gives up after
+// ~timeout_ns raises it here AND in both neighbours' flag blocks, every wait returns at once
+// when it finds it raised (at entry or while spinning), so one stalled rank stops the whole
+// ring within one time-out instead of one time-out per remaining wait; lbm_sync reports it.
+__global__ void flag_wait_kernel(volatile int *flags, volatile int *up_abort, volatile int *dn_abort, int epoch, unsigned long long timeout_ns)
 {
+	if (flags[3]) return;
 	unsigned long long t0;
 	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
 	while (flags[0] < epoch || flags[1] < epoch) {
 		unsigned long long t;
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-		if (t - t0 > timeout_ns) { flags[3] = 1; break; }
+		if (flags[3] || t - t0 > timeout_ns) {
+			flags[3] = 1; *up_abort = 1; *dn_abort = 1;
+			break;
+		}
 		__nanosleep(200);
 	}
 	__threadfence_system();

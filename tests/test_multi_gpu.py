@@ -20,4 +20,7 @@ def test_ring_over_gpus_equals_single_gpu():
            "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tools", "mgpu_check.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
-    assert "MISMATCH" not in out.stdout and out.stdout.count("BIT-EXACT") == 5
+    import re
+    m = re.search(r"\[mgpu\] (\d+)/(\d+) cases BIT-EXACT", out.stdout)
+    assert m and m.group(1) == m.group(2) and int(m.group(2)) >= 15, out.stdout[-3000:]
+    assert "MISMATCH" not in out.stdout

@@ -23,7 +23,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
-    ok = True
+    ok, nsame = True, 0
     CASES = [("dp", "p2p", 803, 2000, False), ("sp", "p2p", 803, 2000, False), ("dp", "staged", 401, 1000, False),
              ("dp", "p2p", world, 64, False), ("sp", "p2p", 2 * world + 1, 264, False),
              # one buffer per slab, in-place kernels: phase-1 boundary rows store into the neighbour's OWNED rows
@@ -65,6 +65,7 @@ def main():
             if not inplace:
                 same = same and np.concatenate(parts_b, axis=1).tobytes() == want_b.tobytes()
             ok &= same
+            nsame += int(same)
             print(f"[mgpu] {prec} {transport}{' in-place' if inplace else ''}{' ' + str(inplace) if isinstance(inplace, dict) else ''} {nx}x{ny} over {world} GPUs: {'BIT-EXACT' if same else 'MISMATCH'} vs single GPU (A/B) "
                   f"(Re {re!r} vs {want_re!r}; {dt:.2f} s)", flush=True)
             if not same:
@@ -72,6 +73,8 @@ def main():
                 print("   first differing elements (s,i,j):", bad[:5].tolist(), flush=True)
         dl.close()
         dist.barrier()
+    if rank == 0:
+        print(f"[mgpu] {nsame}/{len(CASES)} cases BIT-EXACT over {world} GPUs", flush=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()

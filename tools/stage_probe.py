@@ -1,6 +1,5 @@
-"""lbm_tuning.stage_smem (next row staged in shared memory by cp.async, stream_collide_aa_staged_kernel) against the
-one-row-per-thread kernels: bits first, then MLUPS over rows_per_thread.  NOT RUN YET (round 1 ended without GPU budget):
-first thing to run in round 2 --   gpurun -- 'LBM_TEST_EXPERIMENTAL=1 python -m pytest tests -m gpu -q -k staged; python tools/stage_probe.py'"""
+"""lbm_tuning.stage_smem (next row staged in shared memory by cp.async, stream_collide_aa_staged_kernel; 2 = TMA bulk copies in
+phase 2) against the one-row-per-thread kernels: bits first, then MLUPS over rows_per_thread."""
 import json
 import os
 import sys
@@ -26,8 +25,8 @@ for prec, nx, ny, T in (("dp", 400, 2000, 4000), ("dp", 400, 4000, 2000), ("sp",
         rec = dict(prec=prec, nx=nx, ny=ny, engine="default", tb_depth=d["tb_depth"], vec=d["vec"], mlups=round(nx * ny * T / ms / 1e3, 1))
         out.append(rec); print(json.dumps(rec), flush=True)
         init(); lat.run(32); want = lat.download("A")
-        for mode, blk in ((1, 128), (1, 64), (1, 256), (2, 128), (2, 64)):     # 1: cp.async both phases; 2: TMA bulk copies in phase 2
-            for rpt in (2, 3, 4, 6, 8, 16):
+        for mode, blk in ((1, 128), (1, 256), (2, 128), (2, 64)):     # 1: cp.async both phases; 2: TMA bulk copies in phase 2
+            for rpt in (4, 8, 16):
                 lat.set_tuning(vec=1, rows_per_thread=rpt, stage_smem=mode, block=blk)
                 init(); lat.run(32)
                 same = bool(np.array_equal(lat.download("A").view(np.uint8), want.view(np.uint8)))
