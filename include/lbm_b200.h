@@ -40,7 +40,8 @@ enum {
 	LBM_ERR_ARG = 1,    /* bad argument (odd step count, mask value not 0/1, ...) */
 	LBM_ERR_CUDA = 2,   /* CUDA runtime/driver error, text in lbm_last_error() */
 	LBM_ERR_STATE = 3,  /* call order (e.g. run before upload/initialize) */
-	LBM_ERR_IO = 4      /* PrintLattice could not open its file */
+	LBM_ERR_IO = 4,     /* PrintLattice / lbm_load_walls could not open or parse its file */
+	LBM_ERR_FPE = 5     /* lbm_check_finite found NaN/Inf (stands in for the reference's FP traps, LB.c:129) */
 };
 
 enum { LBM_BUF_A = 0, LBM_BUF_B = 1 };
@@ -72,6 +73,11 @@ typedef struct {
 	int channel_walls;           /* rows 0 and nx-1 solid (LB.c:575-578) */
 	int bar_i0, bar_i1, bar_j0, bar_j1; /* solid box rows [i0,i1) x cols [j0,j1) (LB.c:567-573); empty if i0>=i1 */
 	long long disc_ci, disc_cj, disc_r; /* solid disc (i-ci)^2+(j-cj)^2 <= r^2 in integers; r<0: none */
+	unsigned perturb_seed;       /* 0: uniform density rho0 (LB.c:583-591).  != 0: a closed-form rough initial state for
+	                                full-size parity checks, rho(i,j) = rho0*(1 + amp*(h/2^32 - 1/2)) with h the 32-bit
+	                                integer hash of (global row, column, seed); fA = rho*omega_s, every operation rounded
+	                                once in real_t so that a host can reproduce any window of it bit for bit */
+	real_t perturb_amp;
 } lbm_scene;
 
 int lbm_sizeof_real(void);            /* 8 (dp library) or 4 (sp library) */
@@ -96,6 +102,10 @@ int lbm_download(lbm_ctx *ctx, real_t *fA, real_t *fB, char *walls_out, int ldy)
  * would own): planes of nx_local rows, the slab's first row at row 0. */
 int lbm_upload_slab(lbm_ctx *ctx, const real_t *fA, const real_t *fB, const char *walls, int ldy);
 int lbm_download_slab(lbm_ctx *ctx, real_t *fA, real_t *fB, char *walls_out, int ldy);
+
+/* A rectangular window of buffer `buf`: local rows [r0,r1) x columns [j0,j1) of this slab into a dense
+ * out[9][r1-r0][j1-j0] (the reference has only whole-array observers; lattices of tens of GB want windows). */
+int lbm_download_window(lbm_ctx *ctx, int buf, int r0, int r1, int j0, int j1, real_t *out);
 
 /* ---- the timestep path ---- */
 /* DoTimeStep (LB.c:186-210): Source(A); A->B; Source(B); B->A.  Asynchronous. */
@@ -127,6 +137,16 @@ int lbm_macroscopic(lbm_ctx *ctx, real_t *rho, real_t *ux, real_t *uy);
 /* PrintLattice (LB.c:610-639): CSV of u_x^2+u_y^2, "%.10lf", ", " separated, one lattice
  * row per line.  `path` replaces the hard-wired data/<timeStep>.csv. */
 int lbm_print_lattice(lbm_ctx *ctx, const char *path);
+
+/* 64-bit checksum of buffer `buf` over this slab's elements: the sum (mod 2^64) of
+ * mix64(bits(f[s][i][j]) ^ mix64((s*NX + i)*NY + j)) with GLOBAL row i -- the checksums of the slabs of a ring add up to
+ * the single-GPU value, whatever the partition.  (No reference counterpart: a size-independent parity property for the
+ * lattices too large to download and compare.) */
+int lbm_checksum(lbm_ctx *ctx, int buf, unsigned long long *sum);
+/* Stand-in for the reference's floating-point traps (feenableexcept(FE_ALL_EXCEPT & ~FE_INEXACT), LB.c:129: the
+ * reference aborts on NaN, overflow and division by zero): counts the non-finite populations of buffer A;
+ * LBM_ERR_FPE if there are any.  *nonfinite may be NULL.  Synchronous; one pass over the lattice. */
+int lbm_check_finite(lbm_ctx *ctx, unsigned long long *nonfinite);
 
 /* ---- slab decomposition / halo exchange (README.md:44-53; no reference source) ---- */
 typedef struct {

@@ -15,7 +15,7 @@ BLOB_BYTES = 256
 DTYPE = {"dp": np.float64, "sp": np.float32}
 CREAL = {"dp": ctypes.c_double, "sp": ctypes.c_float}
 
-OK, ERR_ARG, ERR_CUDA, ERR_STATE, ERR_IO = range(5)
+OK, ERR_ARG, ERR_CUDA, ERR_STATE, ERR_IO, ERR_FPE = range(6)
 
 
 class LbmError(RuntimeError):
@@ -34,7 +34,8 @@ def _structs(real):
         _fields_ = [("rho0", real), ("channel_walls", ctypes.c_int),
                     ("bar_i0", ctypes.c_int), ("bar_i1", ctypes.c_int),
                     ("bar_j0", ctypes.c_int), ("bar_j1", ctypes.c_int),
-                    ("disc_ci", ctypes.c_longlong), ("disc_cj", ctypes.c_longlong), ("disc_r", ctypes.c_longlong)]
+                    ("disc_ci", ctypes.c_longlong), ("disc_cj", ctypes.c_longlong), ("disc_r", ctypes.c_longlong),
+                    ("perturb_seed", ctypes.c_uint), ("perturb_amp", real)]
 
     class SlabInfo(ctypes.Structure):
         _fields_ = [("nx_local", ctypes.c_int), ("ny", ctypes.c_int), ("row_lo", ctypes.c_int), ("row_hi", ctypes.c_int),
@@ -55,10 +56,10 @@ def _structs(real):
 # every symbol include/lbm_b200.h declares (tests check the library exports each one)
 SYMBOLS = [
     "lbm_sizeof_real", "lbm_last_error", "lbm_version", "lbm_create", "lbm_destroy",
-    "lbm_scene_reference", "lbm_initialize_arrays", "lbm_upload", "lbm_download", "lbm_upload_slab", "lbm_download_slab",
+    "lbm_scene_reference", "lbm_initialize_arrays", "lbm_upload", "lbm_download", "lbm_upload_slab", "lbm_download_slab", "lbm_download_window",
     "lbm_do_timestep", "lbm_run", "lbm_run_timed", "lbm_apply_source", "lbm_stream_collide", "lbm_sync",
     "lbm_compute_reynolds", "lbm_reynolds_column", "lbm_reynolds_from_column", "lbm_macroscopic",
-    "lbm_print_lattice", "lbm_slab_info_get", "lbm_ipc_export", "lbm_ipc_connect", "lbm_connect_local",
+    "lbm_print_lattice", "lbm_checksum", "lbm_check_finite", "lbm_slab_info_get", "lbm_ipc_export", "lbm_ipc_connect", "lbm_connect_local",
     "lbm_group_run", "lbm_halo_pack", "lbm_halo_unpack", "lbm_step_rows", "lbm_stream_handle",
     "lbm_stream_join", "lbm_set_tuning", "lbm_get_tuning", "lbm_kernel_launches", "lbm_tb_schedule",
 ]
@@ -95,10 +96,12 @@ class Lib:
             "lbm_destroy": [vp], "lbm_initialize_arrays": [vp, ctypes.POINTER(self.Scene)],
             "lbm_upload": [vp, vp, vp, vp, ci], "lbm_download": [vp, vp, vp, vp, ci],
             "lbm_upload_slab": [vp, vp, vp, vp, ci], "lbm_download_slab": [vp, vp, vp, vp, ci],
+            "lbm_download_window": [vp, ci, ci, ci, ci, ci, vp],
             "lbm_do_timestep": [vp], "lbm_run": [vp, ci], "lbm_run_timed": [vp, ci, ctypes.POINTER(ctypes.c_float)],
             "lbm_apply_source": [vp, ci], "lbm_stream_collide": [vp, ci], "lbm_sync": [vp],
             "lbm_compute_reynolds": [vp, ctypes.POINTER(self.real)], "lbm_reynolds_column": [vp, vp, vp],
             "lbm_macroscopic": [vp, vp, vp, vp], "lbm_print_lattice": [vp, ctypes.c_char_p],
+            "lbm_checksum": [vp, ci, ctypes.POINTER(ctypes.c_ulonglong)], "lbm_check_finite": [vp, ctypes.POINTER(ctypes.c_ulonglong)],
             "lbm_slab_info_get": [vp, ctypes.POINTER(self.SlabInfo)], "lbm_ipc_export": [vp, vp],
             "lbm_ipc_connect": [vp, vp, vp], "lbm_connect_local": [vp, vp, vp],
             "lbm_group_run": [ctypes.POINTER(vp), ci, ci], "lbm_halo_pack": [vp, ci, vp, vp],

@@ -167,6 +167,7 @@ lbm_scene lbm_scene_reference(void)
 	s.bar_i0 = 20; s.bar_i1 = 220;        /* LB.c:567 */
 	s.bar_j0 = 100; s.bar_j1 = 105;       /* LB.c:568-572 */
 	s.disc_ci = s.disc_cj = 0; s.disc_r = -1;
+	s.perturb_seed = 0; s.perturb_amp = REAL_T(0.0);
 	return s;
 }
 
@@ -994,7 +995,8 @@ int lbm_initialize_arrays(lbm_ctx *c, const lbm_scene *scene)
 	CK(cudaGetLastError());
 	/* INITIALDENSITY * OMEGA_s in real_t (LB.c:583-591) */
 	scene_fill_kernel<real_t><<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(
-		c->f[0], c->f[1] /* nullptr when in place */, c->plane, c->ldy, c->nxl, c->ny, scene->rho0 * c->w0, scene->rho0 * c->w14, scene->rho0 * c->w58);
+		c->f[0], c->f[1] /* nullptr when in place */, c->plane, c->ldy, c->nxl, c->ny, c->cfg.row_lo, scene->rho0, c->w0, c->w14, c->w58,
+		scene->perturb_seed, scene->perturb_amp);
 	CK(cudaGetLastError());
 	c->launches += 2;
 	c->has_state = 1;
@@ -1084,6 +1086,24 @@ static int download_impl(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, in
 		CK(cudaMemcpy2DAsync(walls_out + row0, (size_t)ldy, dwalls, ldc, (size_t)c->ny, (size_t)c->nxl, cudaMemcpyDeviceToHost, st));
 		CK(cudaFreeAsync(dwalls, st));
 	}
+	CK(cudaStreamSynchronize(st));
+	return LBM_OK;
+}
+
+int lbm_download_window(lbm_ctx *c, int buf, int r0, int r1, int j0, int j1, real_t *out)
+{
+	if (!c || !out || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_download_window: bad argument");
+	if (buf == 1 && c->inplace) return fail(LBM_ERR_STATE, "lbm_download_window: an in-place context has no buffer B");
+	if (r0 < 0 || r1 > c->nxl || r0 >= r1 || j0 < 0 || j1 > c->ny || j0 >= j1)
+		return fail(LBM_ERR_ARG, "lbm_download_window: rows [%d,%d) of %d, columns [%d,%d) of %d", r0, r1, c->nxl, j0, j1, c->ny);
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	cudaStream_t st = c->stream[0];
+	const size_t w = (size_t)(j1 - j0), h = (size_t)(r1 - r0);
+	for (int s = 0; s < 9; s++)
+		CK(cudaMemcpy2DAsync(out + (size_t)s * h * w, w * sizeof(real_t),
+		                     c->f[buf] + s * c->plane + (size_t)(r0 + 1) * c->ldy + j0, (size_t)c->ldy * sizeof(real_t),
+		                     w * sizeof(real_t), h, cudaMemcpyDeviceToHost, st));
 	CK(cudaStreamSynchronize(st));
 	return LBM_OK;
 }
@@ -1309,6 +1329,46 @@ int lbm_print_lattice(lbm_ctx *c, const char *path)
 		fwrite(line.data(), 1, pos, fp);
 	}
 	fclose(fp);
+	return LBM_OK;
+}
+
+static int reduce_u64(lbm_ctx *c, int buf, int what, unsigned long long *out)
+{
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	cudaStream_t st = c->stream[0];
+	unsigned long long *d = nullptr;
+	CK(cudaMallocAsync(&d, sizeof *d, st));
+	CK(cudaMemsetAsync(d, 0, sizeof *d, st));
+	const size_t total = (size_t)c->nxl * c->ny;
+	size_t grid = (total + 255) / 256;
+	const size_t cap = (size_t)sm_count(c->cfg.device) * 8;              /* one resident wave, grid-stride */
+	if (grid > cap) grid = cap;
+	if (what == 0) checksum_kernel<real_t><<<(unsigned)grid, 256, 0, st>>>(c->f[buf], c->plane, c->ldy, c->nxl, c->ny, c->cfg.row_lo, c->cfg.nx, d);
+	else nonfinite_kernel<real_t><<<(unsigned)grid, 256, 0, st>>>(c->f[buf], c->plane, c->ldy, c->nxl, c->ny, d);
+	CK(cudaGetLastError());
+	c->launches++;
+	CK(cudaMemcpyAsync(out, d, sizeof *d, cudaMemcpyDeviceToHost, st));
+	CK(cudaFreeAsync(d, st));
+	CK(cudaStreamSynchronize(st));
+	return LBM_OK;
+}
+
+int lbm_checksum(lbm_ctx *c, int buf, unsigned long long *sum)
+{
+	if (!c || !sum || (buf != 0 && buf != 1)) return fail(LBM_ERR_ARG, "lbm_checksum: bad argument");
+	if (buf == 1 && c->inplace) return fail(LBM_ERR_STATE, "lbm_checksum: an in-place context has no buffer B");
+	return reduce_u64(c, buf, 0, sum);
+}
+
+int lbm_check_finite(lbm_ctx *c, unsigned long long *nonfinite)
+{
+	if (!c) return fail(LBM_ERR_ARG, "lbm_check_finite: null ctx");
+	unsigned long long n = 0;
+	int rc;
+	if ((rc = reduce_u64(c, LBM_BUF_A, 1, &n))) return rc;
+	if (nonfinite) *nonfinite = n;
+	if (n) return fail(LBM_ERR_FPE, "lbm_check_finite: %llu non-finite populations in buffer A (the reference would have trapped, LB.c:129)", n);
 	return LBM_OK;
 }
 

@@ -1410,19 +1410,92 @@ __global__ void scene_mask_kernel(uint32_t *mask, SceneDev sc, int row_lo, int n
 	}
 	mask[g] = bits;
 }
-// fA = rho0*omega_s at every owned site (walls included), fB = 0 (LB.c:580-603); j < ny only
-template <typename T>
-__global__ void scene_fill_kernel(T *fA, T *fB, size_t plane, int ldy, int nxl, int ny, T v0, T v14, T v58)
+// 32-bit integer hash (lowbias32) -- the closed-form density perturbation of lbm_scene.perturb_seed
+__host__ __device__ __forceinline__ uint32_t hash32(uint32_t x)
 {
+	x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+	return x;
+}
+// fA = rho*omega_s at every owned site (walls included), fB = 0 (LB.c:580-603); j < ny only.
+// rho = rho0 (LB.c:56), or, with a perturbation seed, rho0 * (1 + amp * (u - 1/2)) with u = h / 2^32 in [0,1) from the
+// integer hash h of (global row, column, seed): a closed-form rough initial state, every operation one rounding in T
+// (geometry.perturbed_rest evaluates the same expression with numpy for any window of the lattice).
+template <typename T>
+__global__ void scene_fill_kernel(T *fA, T *fB, size_t plane, int ldy, int nxl, int ny, int row_lo, T rho0, T w0, T w14, T w58, uint32_t seed, T amp)
+{
+	typedef fp<T> A;
 	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= (size_t)nxl * ny) return;
 	const int r = (int)(g / ny), j = (int)(g % ny);
 	const size_t o = (size_t)(r + 1) * ldy + j;
+	T rho = rho0;
+	if (seed) {
+		const uint32_t h = hash32((uint32_t)(row_lo + r) * 0x9E3779B1u ^ hash32((uint32_t)j + seed));
+		const T u = A::mul((T)h, T(1.0 / 4294967296.0));             /* exact scaling; (T)h rounds to nearest in SP */
+		rho = A::mul(rho0, A::add(T(1), A::mul(amp, A::sub(u, T(0.5)))));
+	}
 #pragma unroll
 	for (int s = 0; s < 9; s++) {
-		fA[o + s * plane] = s == 0 ? v0 : (s <= 4 ? v14 : v58);
+		fA[o + s * plane] = A::mul(rho, s == 0 ? w0 : (s <= 4 ? w14 : w58));
 		if (fB) fB[o + s * plane] = T(0);
 	}
+}
+
+// Decomposition-invariant 64-bit checksum of one buffer: the sum (mod 2^64) over every owned element (s, global row i,
+// column j < ny) of mix64(bit pattern ^ mix64(global element index)), global index = (s*NX + i)*NY + j.  Addition is
+// commutative, so the checksums of the slabs of a ring add up to the single-GPU value whatever the partition and the
+// reduction order; position enters through the inner mix, so permuted or shifted data does not cancel.
+__host__ __device__ __forceinline__ unsigned long long mix64(unsigned long long z)
+{
+	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+	z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+	return z ^ (z >> 31);
+}
+__device__ __forceinline__ unsigned long long bits_of(double v) { return (unsigned long long)__double_as_longlong(v); }
+__device__ __forceinline__ unsigned long long bits_of(float v) { return (unsigned long long)__float_as_uint(v); }
+template <typename T>
+__global__ void __launch_bounds__(256)
+checksum_kernel(const T *f, size_t plane, int ldy, int nxl, int ny, int row_lo, int nx_global, unsigned long long *out)
+{
+	unsigned long long acc = 0;
+	const size_t total = (size_t)nxl * ny;
+	for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
+		const int r = (int)(g / ny), j = (int)(g % ny);
+		const T *site = f + (size_t)(r + 1) * ldy + j;
+#pragma unroll
+		for (int s = 0; s < 9; s++) {
+			const unsigned long long idx = ((unsigned long long)s * nx_global + (unsigned long long)(row_lo + r)) * ny + j;
+			acc += mix64(bits_of(site[(size_t)s * plane]) ^ mix64(idx));
+		}
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, d);
+	__shared__ unsigned long long part[8];
+	if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		unsigned long long t = 0;
+		for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += part[w];
+		atomicAdd(out, t);
+	}
+}
+
+// isfinite guard (the reference traps NaN / overflow / division by zero with feenableexcept, LB.c:129): counts the
+// owned elements of one buffer that are not finite
+template <typename T>
+__global__ void __launch_bounds__(256)
+nonfinite_kernel(const T *f, size_t plane, int ldy, int nxl, int ny, unsigned long long *out)
+{
+	unsigned int bad = 0;
+	const size_t total = (size_t)nxl * ny;
+	for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
+		const int r = (int)(g / ny), j = (int)(g % ny);
+		const T *site = f + (size_t)(r + 1) * ldy + j;
+#pragma unroll
+		for (int s = 0; s < 9; s++) bad += !isfinite(site[(size_t)s * plane]);
+	}
+	bad = __reduce_add_sync(0xffffffffu, bad);
+	if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out, (unsigned long long)bad);
 }
 
 // walls chars [nxl][ldc] -> bit words; *bad is set if a value other than 0/1 is seen

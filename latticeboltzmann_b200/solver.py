@@ -99,6 +99,12 @@ class Lattice:
         self._call("lbm_download_slab", a, b, None, self.ny)
         return out
 
+    def download_window(self, r0, r1, j0, j1, which="A"):
+        """(9, r1-r0, j1-j0): local rows [r0,r1) x columns [j0,j1) of this slab (lbm_download_window)."""
+        out = np.zeros((9, r1 - r0, j1 - j0), dtype=self.dtype)
+        self._call("lbm_download_window", 0 if which == "A" else 1, int(r0), int(r1), int(j0), int(j1), _ptr(out))
+        return out
+
     def download_walls(self, ldy=None):
         ldy = self.ny if ldy is None else ldy
         out = np.zeros((self.nx, ldy), dtype=np.int8)
@@ -151,6 +157,18 @@ class Lattice:
 
     def PrintLattice(self, path):
         self._call("lbm_print_lattice", str(path).encode())
+
+    def checksum(self, which="A"):
+        """Decomposition-invariant 64-bit checksum of this slab's part of a buffer (lbm_checksum); the slabs of a ring
+        add up (mod 2**64) to the single-GPU value.  geometry.checksum is the numpy statement of the same sum."""
+        out = ctypes.c_ulonglong()
+        self._call("lbm_checksum", 0 if which == "A" else 1, ctypes.byref(out))
+        return int(out.value)
+
+    def check_finite(self):
+        """Raises LbmError(ERR_FPE) if buffer A holds NaN/Inf (the reference traps instead, LB.c:129)."""
+        n = ctypes.c_ulonglong()
+        self._call("lbm_check_finite", ctypes.byref(n))
 
     # ---- slabs / tuning ----------------------------------------------------------------------------
     def slab_info(self):

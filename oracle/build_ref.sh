@@ -94,5 +94,22 @@ build_fast float  sp 400 4000 1000
 build_fast float  sp 400 4000 10000
 build_fast double dp 800 4000 1000
 
+# The weak-scaling unit (BASELINE configs[4], 8192x32768 per GPU) for `bench.py --impl reference`: 9*NX*NY = 2.4e9
+# elements overflow the reference's int indexing (LB.c:72 `I()`, LB.c:136 `int allocSize`), so this one build also
+# widens exactly those two expressions to size_t (SURVEY.md 8(c) patch (5)); nothing else changes.
+build_fast_big() { # prec tag NX NY STEPS
+	patch_fixed "$1_avx" "$3" "$4" "$5" | \
+	sed -e 's|^#define I(i,j, speed) ((speed)\*NX\*NYPADDED + (i)\*NYPADDED + (j))|#define I(i,j, speed) ((size_t)(speed)*NX*NYPADDED + (size_t)(i)*NYPADDED + (j))|' \
+	    -e 's|int allocSize = NX \* NYPADDED \* NSPEEDS;|size_t allocSize = (size_t)NX * NYPADDED * NSPEEDS;|' \
+	    -e 's|walls = _mm_malloc(NX \* NYPADDED \* sizeof \*walls, 32);|walls = _mm_malloc((size_t)NX * NYPADDED * sizeof *walls, 32);|' | \
+		$CC -x c - -I"$REF/src" $FAST -o "$OUT/lbref_fast_$2_$3x$4_$5" -lrt -lm
+}
+build_fast_big double dp 8192 32768 10
+build_fast_big float  sp 8192 32768 10
+# the same patch on a small lattice: tests/test_oracle_golden.py checks it prints the Reynolds number of the unpatched build
+build_fast_big double dp 400 2000 1000
+mv "$OUT/lbref_fast_dp_400x2000_1000" "$OUT/lbref_fastbig_dp_400x2000_1000"
+build_fast double dp 400 2000 1000
+
 echo "build_ref.sh: built into $OUT:" >&2
 ls "$OUT" >&2

@@ -51,6 +51,8 @@ typedef struct {
 	int ldy;         /* row stride in elements = NYPADDED (LB.c:71) */
 	int vw;          /* emulated VECWIDTH: 1 serial, 2/4 SSE, 4/8 AVX */
 	real tau, accel, rho0;
+	int source_col;  /* column ApplySource acts on: 0 in the reference (LB.c:500-515).  Test windows cut out of a larger
+	                    lattice (tests/test_gpu_fullsize.py) put the lattice's column 0 elsewhere, or nowhere (-1). */
 } lbo_params;
 
 int lbo_sizeof_real(void) { return (int)sizeof(real); }
@@ -229,16 +231,18 @@ void lbo_stream_collide_vec(const lbo_params *p, int jmin, int jmax,
 			collide_group(p, src, dst, walls, w, i, j);
 }
 
-/* body force on column 0, in place; LB.c:489-518 */
+/* body force on column 0 (p->source_col), in place; LB.c:489-518 */
 void lbo_apply_source(const lbo_params *p, real *f, const char *walls)
 {
 	real w[Q];
 	weights(w);
 	const real a14 = p->accel * w[1], a58 = p->accel * w[5];
+	const int c = p->source_col;
+	if (c < 0 || c >= p->ny) return;
 	for (int i = 0; i < p->nx; i++) {
-		if (walls[(size_t)i * p->ldy] != 0) continue;
-		real *f1 = &f[at(p, 1, i, 0)], *f3 = &f[at(p, 3, i, 0)], *f5 = &f[at(p, 5, i, 0)];
-		real *f6 = &f[at(p, 6, i, 0)], *f7 = &f[at(p, 7, i, 0)], *f8 = &f[at(p, 8, i, 0)];
+		if (walls[(size_t)i * p->ldy + c] != 0) continue;
+		real *f1 = &f[at(p, 1, i, c)], *f3 = &f[at(p, 3, i, c)], *f5 = &f[at(p, 5, i, c)];
+		real *f6 = &f[at(p, 6, i, c)], *f7 = &f[at(p, 7, i, c)], *f8 = &f[at(p, 8, i, c)];
 		if (*f6 - a58 > R(0.0) && *f3 - a14 > R(0.0) && *f7 - a58 > R(0.0)) {
 			*f6 -= a58;  *f3 -= a14;  *f7 -= a58;
 			*f5 += a58;  *f1 += a14;  *f8 += a58;

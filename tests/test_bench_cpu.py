@@ -22,7 +22,8 @@ def test_reference_arm_prints_the_contract_line():
     exe = os.path.join(ROOT, "oracle", "_ref", "lbref_fast_dp_400x4000_1000")
     if not os.path.exists(exe):
         pytest.skip("oracle/_ref not built here (sh oracle/build_ref.sh needs /root/reference)")
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                        "--reference-lattice", "small"],      # the default (8192x32768, 39 GB of host memory) is for the GPU box
                        capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert p.returncode == 0, p.stderr[-500:]
     lines = [ln for ln in p.stdout.splitlines() if ln.strip()]

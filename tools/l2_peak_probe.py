@@ -1,40 +1,32 @@
 """What the L2 of this B200 delivers to a streaming kernel whose working set is resident: the roof of the temporally
-blocked in-place engine (its tiles live in L2 for k timesteps, HBM is not what binds it -- VERDICT r1, weak 7).
+blocked in-place engine (its tiles live in L2 for k timesteps; HBM is not what binds it -- VERDICT r1, weak 7).
 
-Two probes, CUDA events, best of N after warm-up:
-  copy   b.copy_(a) over a working set of W MB (a and b together), repeated back to back; bytes = read + write.
-         W from 8 MB to 512 MB: the plateau below ~60 MB is the L2 roof, the tail is HBM (cf. MEASURED_PEAKS.json hbm_gbs).
-  lbm    the library's own local in-place phase (phase 2: 9 aligned loads + 9 aligned stores per site, no neighbours)
-         on lattices of the same working-set sizes -- the same access shape as the product kernel.
-Output: one JSON line per point and gpurun_out/l2_peak.json; profiles/ keeps the copy bench.py reads (`l2_gbs`).
+  tools/probe/l2_probe.cu   purpose-written kernels, 128-bit accesses, CUDA events over back-to-back launches:
+                            read / copy / in-place update over working sets of 8 .. 512 MB.  `update` (one read + one
+                            write of the same lines) is the access shape of the in-place LBM phases; the plateau of
+                            read + write GB/s below ~60 MB is the L2 roof, the tail is HBM (cf. MEASURED_PEAKS.json).
+  lbm phases                the library's own in-place phases on lattices of the same working-set sizes, for comparison.
+Output: JSON lines and gpurun_out/l2_peak.json; the copy bench.py reads (key `l2_gbs`) is profiles/l2_peak.json.
 """
+import ctypes
 import json
 import os
+import subprocess
 import sys
-
-import torch
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+MODES = {0: "read", 1: "copy", 2: "update"}
 
 
-def copy_probe(mb, reps=200):
-    n = int(mb * 1e6 / 2 / 8)
-    a = torch.ones(n, dtype=torch.float64, device="cuda")
-    b = torch.empty_like(a)
-    for _ in range(20):
-        b.copy_(a)
-    best = 1e9
-    for _ in range(5):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        e0.record()
-        for _ in range(reps):
-            b.copy_(a)
-        e1.record()
-        torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1) / reps)
-    return 2 * n * 8 / (best * 1e-3) / 1e9
+def load_probe():
+    so = os.path.join(ROOT, "tools", "probe", "libl2probe.so")
+    if not os.path.exists(so):
+        subprocess.run(["make", "-s", "-C", os.path.dirname(so)], check=True)
+    lib = ctypes.CDLL(so)
+    lib.l2probe.argtypes = [ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
+    return lib
 
 
 def lbm_probe(prec, nx, ny, reps=400):
@@ -49,10 +41,6 @@ def lbm_probe(prec, nx, ny, reps=400):
             best = 1e9
             for _ in range(3):
                 lat.sync()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                # the library launches on its own stream: bracket with a device-wide sync and time on the host side of it
-                import time
-                torch.cuda.synchronize()
                 t0 = time.perf_counter()
                 for _ in range(reps):
                     lat._call("lbm_step_rows", phase - 1, 0, nx, 1, 0)
@@ -65,22 +53,33 @@ def lbm_probe(prec, nx, ny, reps=400):
 
 
 def main():
-    res = {"copy": [], "lbm": []}
-    for mb in (8, 16, 24, 32, 40, 48, 56, 64, 80, 96, 128, 192, 256, 512):
-        rec = {"working_set_mb": mb, "gbs": round(copy_probe(mb), 1)}
-        res["copy"].append(rec)
-        print(json.dumps(rec), flush=True)
-    for prec, nx, ny in (("dp", 100, 2000), ("dp", 200, 2000), ("dp", 300, 2000), ("dp", 400, 2000), ("dp", 400, 4000),
-                         ("sp", 200, 4000), ("sp", 400, 4000), ("sp", 800, 4000)):
+    lib = load_probe()
+    res = {"kernels": [], "lbm": []}
+    for mb in (8, 16, 24, 32, 40, 48, 56, 64, 80, 96, 128, 256, 512):
+        for mode in (0, 1, 2):
+            best = None
+            for block, cps in ((256, 0), (512, 0), (256, 8), (1024, 2)):
+                g = ctypes.c_double()
+                rc = lib.l2probe(int(mb * 1e6), mode, block, cps, 200 if mb <= 128 else 40, ctypes.byref(g))
+                if rc == 0 and (best is None or g.value > best["gbs"]):
+                    best = {"working_set_mb": mb, "mode": MODES[mode], "gbs": round(g.value, 1), "block": block, "ctas_per_sm": cps}
+            res["kernels"].append(best)
+            print(json.dumps(best), flush=True)
+    for prec, nx, ny in (("dp", 200, 2000), ("dp", 300, 2000), ("dp", 400, 2000), ("dp", 400, 4000),
+                         ("sp", 400, 4000), ("sp", 800, 4000)):
         rec = {"prec": prec, "nx": nx, "ny": ny, "working_set_mb": round(9 * nx * ny * (8 if prec == "dp" else 4) / 1e6, 1)}
         rec.update(lbm_probe(prec, nx, ny))
         res["lbm"].append(rec)
         print(json.dumps(rec), flush=True)
-    res["l2_gbs"] = max(r["gbs"] for r in res["copy"] if r["working_set_mb"] <= 48)
-    res["how"] = "torch b.copy_(a) float64, working set (a+b) <= 48 MB, 200 back-to-back copies, best of 5, CUDA events; read+write bytes"
+    upd = [r for r in res["kernels"] if r and r["mode"] == "update" and 24 <= r["working_set_mb"] <= 56]
+    res["l2_gbs"] = max(r["gbs"] for r in upd)
+    res["l2_read_gbs"] = max(r["gbs"] for r in res["kernels"] if r and r["mode"] == "read" and 24 <= r["working_set_mb"] <= 56)
+    res["hbm_update_gbs"] = [r["gbs"] for r in res["kernels"] if r and r["mode"] == "update" and r["working_set_mb"] == 512][0]
+    res["how"] = ("tools/probe/l2_probe.cu: in-place update a[i] = a[i]*c + d (double2 accesses, read + write bytes) over an L2-resident "
+                  "working set of 24-56 MB, 200 back-to-back launches, best of 4, CUDA events; l2_gbs = the best such point")
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(res, open(os.path.join(ROOT, "gpurun_out", "l2_peak.json"), "w"), indent=1)
-    print(json.dumps({"l2_gbs": res["l2_gbs"]}))
+    print(json.dumps({k: res[k] for k in ("l2_gbs", "l2_read_gbs", "hbm_update_gbs")}))
 
 
 if __name__ == "__main__":
