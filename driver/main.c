@@ -9,7 +9,8 @@
  *   lbm_b200_{dp,sp} [NX NY NTIMESTEPS [NGPU [SCENE [DUMP_EVERY [INPLACE]]]]]
  *     SCENE: 0 = InitializeArrays (channel + barrier, LB.c:559-578)
  *            1 = channel + disc obstacle (BASELINE config 3: centre (NX/2, NY/5), radius NX/10)
- *     DUMP_EVERY > 0 writes data/<step>.csv like SAVELATTICE (LB.c:155-159; data/ must exist)
+ *     DUMP_EVERY > 0 writes data/<step>.csv like SAVELATTICE (LB.c:155-159; data/ must exist), one file for the
+ *            whole lattice whatever NGPU
  *     INPLACE = 1 (default): one buffer per slab instead of fA/fB (lbm_config.inplace) -- this main never reads fB
  *            (LB.c:152,157,172-173 take fA), fA after every DoTimeStep is bit-identical, and the steps between two
  *            observation points run temporally blocked in L2; 0 = the reference's fA/fB pair
@@ -74,22 +75,30 @@ static int sync_all(void)
 	return 0;
 }
 
+/* The reference runs with FP traps on (feenableexcept, LB.c:129) and dies on the first NaN / overflow / division by
+ * zero; here every observation point checks the lattice instead (one pass per PRINTSTATSEVERY steps). */
+static int finite_all(void)
+{
+	for (int g = 0; g < NGPU; g++)
+		if (lbm_check_finite(slabs[g], NULL) != LBM_OK) return 1;
+	return 0;
+}
+
 /* ComputeReynolds over the slabs: concatenate the centre column in row order (LB.c:522-547) */
 static int reynolds(real_t *re)
 {
 	real_t *uy = malloc((size_t)NX * sizeof *uy);
 	char *fluid = malloc((size_t)NX);
-	int at = 0;
-	for (int g = 0; g < NGPU; g++) {
+	int at = 0, bad = !uy || !fluid;
+	for (int g = 0; g < NGPU && !bad; g++) {
 		lbm_slab_info info;
-		if (lbm_slab_info_get(slabs[g], &info) != LBM_OK) return 1;
-		if (lbm_reynolds_column(slabs[g], uy + at, fluid + at) != LBM_OK) return 1;
+		bad = lbm_slab_info_get(slabs[g], &info) != LBM_OK || lbm_reynolds_column(slabs[g], uy + at, fluid + at) != LBM_OK;
 		at += info.nx_local;
 	}
-	*re = lbm_reynolds_from_column(uy, fluid, NX, TAU);
+	if (!bad) *re = lbm_reynolds_from_column(uy, fluid, NX, TAU);
 	free(uy);
 	free(fluid);
-	return 0;
+	return bad;
 }
 
 int main(int argc, char **argv)
@@ -100,10 +109,12 @@ int main(int argc, char **argv)
 	if (argc >= 6) scene_id = atoi(argv[5]);
 	if (argc >= 7) dump_every = atoi(argv[6]);
 	if (argc >= 8) inplace = atoi(argv[7]) != 0;
-	if (NGPU < 1 || NGPU > MAXGPU || NX < NGPU || (NTIMESTEPS & 1)) {
-		fprintf(stderr, "usage: %s [NX NY NTIMESTEPS(even) [NGPU [SCENE [DUMP_EVERY]]]]\n", argv[0]);
+	if (NGPU < 1 || NGPU > MAXGPU || NX < NGPU || (NTIMESTEPS & 1) || dump_every < 0) {
+		fprintf(stderr, "usage: %s [NX NY NTIMESTEPS(even) [NGPU [SCENE [DUMP_EVERY [INPLACE]]]]]\n", argv[0]);
 		return EXIT_FAILURE;
 	}
+	/* the loop advances two steps at a time (LB.c:148): an odd SAVELATTICEEVERY fires when n is a multiple of both */
+	if (dump_every & 1) dump_every *= 2;
 
 	/* LB.c:136-137 (the reference prints "%lf.2 MB") */
 	printf("Lattice Size: %dx%d (%.2lf MB per buffer, %s, %d GPU%s%s)\n", NX, NY,
@@ -134,21 +145,22 @@ int main(int argc, char **argv)
 	 * one call; the loop structure and the observation points are the reference's. */
 	double startTime = GetWallTime();
 	int chunk = PRINTSTATSEVERY;
-	if (dump_every > 0 && dump_every < chunk) chunk = dump_every;
+	if (dump_every > 0)                                          /* both kinds of observation point fall on chunk boundaries */
+		for (int a = chunk, b = dump_every; b; ) { int t = a % b; a = b; b = t; chunk = a; }
 	for (int n = 0; n < NTIMESTEPS; n += chunk) {
 		if (n % PRINTSTATSEVERY == 0 && n != 0) {
-			if (sync_all()) return EXIT_FAILURE;
+			if (sync_all() || finite_all()) { fprintf(stderr, "%s\n", lbm_last_error()); return EXIT_FAILURE; }
 			PrintRunStats(n, startTime);
 		}
-		if (dump_every > 0 && n % dump_every == 0 && NGPU == 1) {
+		if (dump_every > 0 && n % dump_every == 0) {
 			char filename[100];
 			sprintf(filename, "data/%d.csv", n);                 /* LB.c:613 */
-			CHECK(lbm_print_lattice(slabs[0], filename));
+			CHECK(lbm_print_lattice_group(slabs, NGPU, filename));
 		}
 		int todo = NTIMESTEPS - n < chunk ? NTIMESTEPS - n : chunk;
 		CHECK(lbm_group_run(slabs, NGPU, todo));                 /* DoTimeStep x todo/2, LB.c:162 */
 	}
-	if (sync_all()) { fprintf(stderr, "%s\n", lbm_last_error()); return EXIT_FAILURE; }
+	if (sync_all() || finite_all()) { fprintf(stderr, "%s\n", lbm_last_error()); return EXIT_FAILURE; }
 	double timeElapsed = GetWallTime() - startTime;
 
 	PrintRunStats(NTIMESTEPS, startTime);                        /* LB.c:172 */

@@ -46,6 +46,20 @@ enum {
 
 enum { LBM_BUF_A = 0, LBM_BUF_B = 1 };
 
+/* y (column) ends of the lattice -- the reference's dead WRAPAROUND macro (LB.c:42-43): "Wrap-around (periodic) or not
+ * (fluid flows out of the domain)".  LBM_Y_PERIODIC is what the reference computes (LB.c:233-234, 337-338).
+ * LBM_Y_OUTFLOW opens both ends: a population that would be pulled from beyond column 0 / NY-1 is taken from the end
+ * column itself (same speed, same row shift: a zero-gradient end), what streams past an end leaves the lattice, and
+ * ApplySource keeps forcing column 0.  The reference has no such code path: parity for it can only be checked against a CPU
+ * restatement of THIS definition ("parity unpinned"). */
+enum { LBM_Y_PERIODIC = 0, LBM_Y_OUTFLOW = 1 };
+
+/* wall mask values (LB.c:140: char per site).  0 and 1 are the reference's; 2 and 3 are the "reflect (slip)" walls its
+ * header comment names (LB.c:21) and never implements: specular reflection instead of reversal, about a wall whose normal
+ * is the x (row) axis -- e.g. the channel walls -- or the y axis.  f0 of a wall site is left untouched either way
+ * (LB.c:246-255).  Parity unpinned like LBM_Y_OUTFLOW. */
+enum { LBM_FLUID = 0, LBM_WALL_BOUNCE = 1, LBM_WALL_SLIP_X = 2, LBM_WALL_SLIP_Y = 3 };
+
 /* The compile-time constants of LB.c:46-56, as run-time fields. */
 typedef struct {
 	int nx, ny;        /* NX, NY (LB.c:46-47): global rows (x, slow) / columns (y, contiguous) */
@@ -65,12 +79,14 @@ typedef struct {
 	                      after every DoTimeStep / even step count is bit-identical to the
 	                      A/B result; buffer B does not exist (fB arguments must be NULL,
 	                      lbm_stream_collide and the staged halo transport are refused). */
+	int boundary_y;    /* LBM_Y_PERIODIC (0, the reference) or LBM_Y_OUTFLOW.  With inplace = 1 open ends need the
+	                      vector kernels on every column (vecwidth > 1 and ny a multiple of it). */
 } lbm_config;
 
 /* Closed-form scenes.  lbm_scene_reference() is InitializeArrays (LB.c:551-606). */
 typedef struct {
 	real_t rho0;                 /* INITIALDENSITY (LB.c:56): fA = rho0*omega_s at rest, fB = 0 */
-	int channel_walls;           /* rows 0 and nx-1 solid (LB.c:575-578) */
+	int channel_walls;           /* 1: rows 0 and nx-1 solid, bounce-back (LB.c:575-578); 2: the same rows as reflect (slip) walls; 0: none */
 	int bar_i0, bar_i1, bar_j0, bar_j1; /* solid box rows [i0,i1) x cols [j0,j1) (LB.c:567-573); empty if i0>=i1 */
 	long long disc_ci, disc_cj, disc_r; /* solid disc (i-ci)^2+(j-cj)^2 <= r^2 in integers; r<0: none */
 	unsigned perturb_seed;       /* 0: uniform density rho0 (LB.c:583-591).  != 0: a closed-form rough initial state for
@@ -93,8 +109,14 @@ int lbm_destroy(lbm_ctx *ctx);
 lbm_scene lbm_scene_reference(void);
 int lbm_initialize_arrays(lbm_ctx *ctx, const lbm_scene *scene);
 /* Host arrays in the reference layout, covering the GLOBAL lattice (nx rows); the slab
- * takes its own rows.  fB may be NULL (zeros, LB.c:593-601).  walls values must be 0/1. */
+ * takes its own rows.  fB may be NULL (zeros, LB.c:593-601).  walls values: LBM_FLUID .. LBM_WALL_SLIP_Y. */
 int lbm_upload(lbm_ctx *ctx, const real_t *fA, const real_t *fB, const char *walls, int ldy);
+/* The wall mask alone (global layout, as for lbm_upload); f is left as it is. */
+int lbm_set_walls(lbm_ctx *ctx, const char *walls, int ldy);
+/* Geometry from a file instead of the hard-wired barrier of LB.c:567-578: text, one lattice row per line, NY entries
+ * per line, each one of the digits 0..3 (the mask values above), optionally separated by blanks and/or commas;
+ * lines starting with '#' are comments; exactly NX rows.  Every slab reads the whole file and keeps its rows. */
+int lbm_load_walls(lbm_ctx *ctx, const char *path);
 /* Copies this slab's rows into global-layout host arrays; either pointer may be NULL.
  * walls_out (optional) receives the unpacked device bitmask as chars. */
 int lbm_download(lbm_ctx *ctx, real_t *fA, real_t *fB, char *walls_out, int ldy);
@@ -137,6 +159,9 @@ int lbm_macroscopic(lbm_ctx *ctx, real_t *rho, real_t *ux, real_t *uy);
 /* PrintLattice (LB.c:610-639): CSV of u_x^2+u_y^2, "%.10lf", ", " separated, one lattice
  * row per line.  `path` replaces the hard-wired data/<timeStep>.csv. */
 int lbm_print_lattice(lbm_ctx *ctx, const char *path);
+/* The same file for a lattice spread over slabs of ONE process (slabs[k] owns the k-th row range, as for
+ * lbm_group_run): SAVELATTICE (LB.c:155-159) of a multi-GPU run. */
+int lbm_print_lattice_group(lbm_ctx **slabs, int nslabs, const char *path);
 
 /* 64-bit checksum of buffer `buf` over this slab's elements: the sum (mod 2^64) of
  * mix64(bits(f[s][i][j]) ^ mix64((s*NX + i)*NY + j)) with GLOBAL row i -- the checksums of the slabs of a ring add up to
@@ -188,18 +213,19 @@ int lbm_stream_handle(lbm_ctx *ctx, int stream_id, void **cuda_stream);
 int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary stream and vice versa */
 
 /* ---- tuning / accounting ---- */
+/* What round 1 measured and dropped (persistent kernel, dataflow kernel, fused step pairs, warp-shuffle neighbours, software
+ * pipelining, capped grids: all slower than the defaults, numbers in DESIGN.md / profiles/) is no longer here; the
+ * shared-memory staged kernels (cp.async / TMA) live in the experiment build only (include/lbm_b200_experimental.h). */
 typedef struct {
-	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = by lattice size (DP: 1 up to 16 Mi sites, else 4; SP: 4) */
-	int block;        /* threads per CTA; 0 = default (the SP in-place kernels run at most 256) */
-	int neighbour;    /* 0 = warp shuffle for the +-1 column element, 1 = direct load */
-	int hints;        /* 0 = default caching, 1 = L1::no_allocate loads + .cs stores */
-	int ctas_per_sm;  /* >0: cap the grid at SMs*ctas_per_sm CTAs (grid-stride), 0 = one pass */
-	int persistent;   /* 1: all steps of a run in ONE cooperative launch, CTAs ordered by per-CTA
-	                     progress counters instead of kernel boundaries; 0 (default): one launch per step */
+	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = by lattice size (DP: 1 up to 16 Mi sites and in place, else 4; SP: 4) */
+	int block;        /* threads per CTA; 0 = default 128 (the SP in-place kernels run at most 256) */
+	int hints;        /* 1: A/B kernel: L1::no_allocate loads + streaming stores; in-place kernels under temporal blocking: the LAST
+	                     level of a macro-step stores with the evict-first policy (its results are not read again while the tile
+	                     is L2-resident).  0 = default caching */
 	int pdl;          /* 1: step kernels are launched with programmatic dependent launch, so the next
 	                     step's CTAs are resident (waiting in griddepcontrol.wait) while this one drains */
-	int graph;        /* >0: steps are replayed from a captured CUDA graph of `graph` step pairs */
-	int tb_depth;     /* in-place single-slab contexts only.  >= 2 (even): temporal blocking in L2 -- the lattice
+	int graph;        /* >0: steps are replayed from a captured CUDA graph of `graph` step pairs (single-slab contexts) */
+	int tb_depth;     /* in-place contexts only.  >= 2 (even): temporal blocking in L2 -- the lattice
 	                     is swept in bands of tb_rows rows, and each band is advanced tb_depth timesteps (one
 	                     kernel launch per band and timestep, band shifted down one row per timestep) while it
 	                     is L2-resident, so HBM sees each site once per tb_depth steps instead of every step.
@@ -207,26 +233,8 @@ typedef struct {
 	                     step t as soon as rows i-1, i, i+1 have taken step t-1.  0 = off (one launch per step). */
 	int tb_rows;      /* band height H in rows; 0 = chosen so that (H + tb_depth) rows take ~45 MB (DP) / 60 MB (SP) */
 	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
-	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 32 KB
-	                     row segments only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
-	int vec_phase1;   /* in-place kernels: sites per thread in phase 1 (the neighbour-access phase); 0 = same as vec */
-	int rows_per_thread; /* in-place kernels: >= 2 = each thread walks that many rows of its launch and loads the
-	                     populations of its next row before relaxing the current one (software pipelining against
-	                     L2 latency); 0/1 = one row per thread */
-	int dataflow;     /* in-place single-slab contexts with temporal blocking in full-width row bands: >= 1 = ONE launch per
-	                     macro-step instead of one per (band, level).  The launches of the schedule are cut into items of one
-	                     row x (block * vec * dataflow) columns, taken by a grid of co-resident CTAs in schedule order; an
-	                     item of level s starts when rows i-1, i, i+1 have finished level s-1 (per-row counters), which is
-	                     all the kernel boundaries guaranteed.  No drain/refill between the short launches.  With it,
-	                     hints = 1 selects L1-cached loads (default: ld.global.cg).  0 = off */
-	int fuse_rows;    /* in-place single-slab contexts: >= 3 = steps 2,3 | 4,5 | ... of a run are taken in pairs by ONE kernel
-	                     (phase 2 of a step and phase 1 of the next): CTAs own tiles of fuse_rows rows x block (64 or 128)
-	                     columns and pass the intermediate populations through shared memory, so a site's nine values
-	                     are loaded and stored once per TWO timesteps; the rims of the tiles take their phase 1 in a
-	                     second, small kernel.  0 = off */
-	int stage_smem;   /* EXPERIMENTAL (compiled, not yet run on a GPU): with rows_per_thread >= 2 and vec 1, the next row's
-	                     populations are staged in shared memory by cp.async instead of a second register set; 2 = phase 2
-	                     moves its row segments with TMA bulk copies (cp.async.bulk + mbarrier) both ways.  0 = off */
+	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 16 KB
+	                     row segments, 32 KB on slabs, only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
@@ -238,8 +246,7 @@ long long lbm_kernel_launches(lbm_ctx *ctx);
  * seam (slabs of a multi-slab ring, multi != 0): bit 0 = wait for both neighbours' previous event before this
  * launch, bit 1 = announce this slab's event after it.  *depth_used = the depth used (single slab: clamped to the
  * ring, 0 = lattice too small, plain stepping).  Returns the number of launches (which may exceed cap; only cap
- * entries are written), -1 on bad arguments.  multi == 2: the order in which the dataflow kernel (lbm_tuning.dataflow)
- * of a single slab takes the same launches. */
+ * entries are written), -1 on bad arguments. */
 int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
 
 #ifdef __cplusplus

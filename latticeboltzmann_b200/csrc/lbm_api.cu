@@ -12,6 +12,10 @@
 #endif
 #include "lbm_b200.h"
 #include "lbm_kernels.cuh"
+#ifdef LBM_EXPERIMENTAL     /* the experiment build (make experimental): shared-memory staged step kernels behind lbm_set_experimental */
+#include "lbm_b200_experimental.h"
+#include "lbm_kernels_experimental.cuh"
+#endif
 
 #include <cstdarg>
 #include <cstdio>
@@ -42,7 +46,6 @@ int fail(int code, const char *fmt, ...)
 	} while (0)
 
 enum { SYNC_SELF = 0, SYNC_LOCAL = 1, SYNC_FLAGS = 2 };
-enum { PROGRESS_SLOTS = 8192 };
 
 
 struct Peer {
@@ -81,23 +84,20 @@ struct lbm_ctx {
 	int n_ipc_opened;
 	lbm_tuning tune;
 	long long launches;
-	int launches_persistent;
 	int has_state;
 	real_t w0, w14, w58, itau, a14, a58;
 	double itau_d;
-	int *progress;               // persistent kernel: per-CTA step counters [PROGRESS_SLOTS] + abort word
+	uint32_t *slip;              // device [2][nxl][ldw]: "reflect" walls with normal x / normal y (mask values 2 / 3)
+	int has_slip;                // any bit set in `slip` (else the kernels are told there is none)
+	int outflow;                 // lbm_config.boundary_y
 	cudaGraphExec_t graph_exec;  // captured `graph_pairs` x (A->B, B->A) steps with the current tuning
 	int graph_pairs;
 	cudaGraphExec_t wf_exec;     // captured wavefront macro-step (wf_k timesteps, bands of wf_h rows)
 	long long wf_launches;       // kernels in that graph
 	int in_wavefront;            // set while run_wavefront enqueues (step kernels may then use PDL on slabs too)
-	/* dataflow kernel (lbm_tuning.dataflow): one launch per macro-step */
-	int *df_cnt;                 // [df_cnt_ints] finished chunks per (level, row)
-	size_t df_cnt_ints;
-	DfLaunch *df_list[2];        // device launch lists: [0] a full macro-step with every tail source (cached), [1] a run's last one
-	size_t df_list_cap[2];
-	int df_nlaunch;              // of df_list[0]; 0 = not built for the current tuning
-	unsigned df_nitems;
+#ifdef LBM_EXPERIMENTAL
+	lbm_experimental exp;
+#endif
 };
 
 namespace {
@@ -120,7 +120,6 @@ void drop_graph(lbm_ctx *c)
 	c->graph_pairs = 0;
 	if (c->wf_exec) cudaGraphExecDestroy(c->wf_exec);
 	c->wf_exec = nullptr;
-	c->df_nlaunch = 0;
 }
 
 int set_device(const lbm_ctx *c) { CK(cudaSetDevice(c->cfg.device)); return LBM_OK; }
@@ -145,6 +144,8 @@ StepParams<real_t> make_params(const lbm_ctx *c, int src, int r0, int r1, int ta
 	p.r0 = r0; p.r1 = r1;
 	p.vw = c->vw;
 	p.tail_source = tail_source;
+	p.outflow = c->outflow;
+	p.slip = c->has_slip ? c->slip : nullptr;
 	p.w0 = c->w0; p.w14 = c->w14; p.w58 = c->w58;
 	p.itau = c->itau; p.itau_d = c->itau_d;
 	p.a14 = c->a14; p.a58 = c->a58;
@@ -179,6 +180,10 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	int vw = cfg->vecwidth ? cfg->vecwidth : VECWIDTH;
 	if (vw != 1 && vw != 2 && vw != 4 && vw != 8) return fail(LBM_ERR_ARG, "lbm_create: vecwidth %d not in {1,2,4,8}", vw);
 	if (cfg->inplace != 0 && cfg->inplace != 1) return fail(LBM_ERR_ARG, "lbm_create: inplace %d not in {0,1}", cfg->inplace);
+	if (cfg->boundary_y != LBM_Y_PERIODIC && cfg->boundary_y != LBM_Y_OUTFLOW) return fail(LBM_ERR_ARG, "lbm_create: boundary_y %d not in {0,1}", cfg->boundary_y);
+	if (cfg->boundary_y == LBM_Y_OUTFLOW && cfg->inplace && (vw == 1 || cfg->ny % vw != 0))
+		return fail(LBM_ERR_ARG, "lbm_create: open y ends with in-place streaming need the vector kernels everywhere (vecwidth > 1 and ny a "
+		                         "multiple of it): the end column's site shares one slot with its in-row neighbour; use inplace = 0");
 	int lo = cfg->row_lo, hi = cfg->row_hi;
 	if (lo == 0 && hi == 0) hi = cfg->nx;
 	if (lo < 0 || hi > cfg->nx || lo >= hi) return fail(LBM_ERR_ARG, "lbm_create: bad slab rows [%d,%d) of %d", lo, hi, cfg->nx);
@@ -219,14 +224,16 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 
 	const size_t fbytes = 9 * c->plane * sizeof(real_t);
 	c->inplace = cfg->inplace ? 1 : 0;
+	c->outflow = cfg->boundary_y == LBM_Y_OUTFLOW;
 	cudaError_t e = cudaMalloc(&c->f[0], fbytes);
 	if (e == cudaSuccess && !c->inplace) e = cudaMalloc(&c->f[1], fbytes);
 	if (e == cudaSuccess) e = cudaMalloc(&c->mask, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMalloc(&c->flags, 4 * sizeof(int));
-	if (e == cudaSuccess) e = cudaMalloc(&c->progress, (PROGRESS_SLOTS + 1) * sizeof(int));
+	if (e == cudaSuccess) e = cudaMalloc(&c->slip, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMemset(c->f[0], 0, fbytes);
 	if (e == cudaSuccess && c->f[1]) e = cudaMemset(c->f[1], 0, fbytes);
 	if (e == cudaSuccess) e = cudaMemset(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
+	if (e == cudaSuccess) e = cudaMemset(c->slip, 0, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMemset(c->flags, 0, 4 * sizeof(int));
 	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaStreamCreateWithFlags(&c->stream[k], cudaStreamNonBlocking);
 	if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming);
@@ -245,14 +252,13 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	c->up.nxl = c->dn.nxl = c->nxl;
 	c->sync_mode = SYNC_SELF;
 	c->wait_timeout_ns = 20ull * 1000 * 1000 * 1000;
+	if (const char *ms = getenv("LBM_WAIT_TIMEOUT_MS"))         /* tests of the ring's abort path */
+		if (atoll(ms) > 0) c->wait_timeout_ns = (unsigned long long)atoll(ms) * 1000ull * 1000ull;
 
 	/* measured best on B200 at every size (profiles/r01_run2): direct neighbour loads, 128-thread CTAs */
 	c->tune.vec = default_vec(c);
 	c->tune.block = 128;
-	c->tune.neighbour = 1;
 	c->tune.hints = 0;
-	c->tune.ctas_per_sm = 0;
-	c->tune.persistent = 0;
 	/* small DP lattices are launch-bound (a step is ~35 us): PDL + graph replay of 10 step pairs measured
 	 * 43.7 vs 41.1 GLUPS at 400x4000 (profiles/r01_run3); no gain for SP or for large lattices */
 	c->tune.pdl = default_small_dp(c);
@@ -296,10 +302,7 @@ int lbm_destroy(lbm_ctx *c)
 	if (c->mask) cudaFree(c->mask);
 	drop_graph(c);
 	if (c->flags) cudaFree(c->flags);
-	if (c->progress) cudaFree(c->progress);
-	if (c->df_cnt) cudaFree(c->df_cnt);
-	for (int i = 0; i < 2; i++)
-		if (c->df_list[i]) cudaFree(c->df_list[i]);
+	if (c->slip) cudaFree(c->slip);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
 	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
 	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -327,32 +330,22 @@ cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, dim3 
 	return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int V, int NB, int HINT>
-cudaError_t launch_vec_inst(const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
-{
-	return launch_kernel(stream_collide_vec_kernel<real_t, V, NB, HINT>, p, dim3(grid), block, st, pdl);
-}
-
-/* in-place (AA) step kernels: phase 1 (from the reference layout) / phase 2 (back to it) */
+/* in-place (AA) step kernels: phase 1 (from the reference layout) / phase 2 (back to it); hint 1 = streaming stores */
 template <int V>
-cudaError_t launch_aa_v(int phase, int pipe, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_aa_v(int phase, int hint, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
 {
-	if (pipe == 1)
+	if (hint)
 		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 1>, p, grid, block, st, pdl)
 		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 1>, p, grid, block, st, pdl);
-	if (pipe == 2 && phase == 1 && V > 1)                        /* aligned accesses + warp shuffles (lbm_tuning.neighbour == 0) */
-		return launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 2>, p, grid, block, st, pdl);
 	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 0>, p, grid, block, st, pdl)
 	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 0>, p, grid, block, st, pdl);
 }
 
 template <int V>
-cudaError_t launch_vec_v(int nb, int hint, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_vec_v(int hint, const StepParams<real_t> &p, unsigned grid, unsigned block, cudaStream_t st, int pdl)
 {
-	if (nb == 0 && hint == 0) return launch_vec_inst<V, 0, 0>(p, grid, block, st, pdl);
-	if (nb == 0 && hint == 1) return launch_vec_inst<V, 0, 1>(p, grid, block, st, pdl);
-	if (nb == 1 && hint == 0) return launch_vec_inst<V, 1, 0>(p, grid, block, st, pdl);
-	return launch_vec_inst<V, 1, 1>(p, grid, block, st, pdl);
+	return hint ? launch_kernel(stream_collide_vec_kernel<real_t, V, 1>, p, dim3(grid), block, st, pdl)
+	            : launch_kernel(stream_collide_vec_kernel<real_t, V, 0>, p, dim3(grid), block, st, pdl);
 }
 
 int sm_count(int device)
@@ -365,11 +358,32 @@ int sm_count(int device)
 	return n;
 }
 
+#ifdef LBM_EXPERIMENTAL
+/* experiment build only: the in-place step with the next row's populations staged in shared memory (cp.async, or TMA bulk
+ * copies for whole-row launches of phase 2); returns cudaErrorNotYetImplemented where it does not apply */
+cudaError_t launch_staged(lbm_ctx *c, int phase, const StepParams<real_t> &p, unsigned rows, unsigned ncols, bool whole_rows, cudaStream_t st, int pdl)
+{
+	if (!c->exp.stage_smem || c->exp.rows_per_thread < 2 || c->nyvec != c->ny || c->outflow) return cudaErrorNotYetImplemented;
+	unsigned blk = (unsigned)c->tune.block > 256u ? 256u : (unsigned)c->tune.block;
+	unsigned gy = (rows + (unsigned)c->exp.rows_per_thread - 1) / (unsigned)c->exp.rows_per_thread;
+	if (gy > 65535u) gy = 65535u;
+	if (phase == 2 && c->exp.stage_smem == 2 && whole_rows && ((size_t)c->ny * sizeof(real_t)) % 16 == 0) {   /* TMA both ways; whole rows of 16-byte units */
+		const unsigned b2 = blk > 128 ? 128 : blk;
+		return launch_kernel(stream_collide_aa_bulk2_kernel<real_t>, p, dim3(((unsigned)c->ny + b2 - 1) / b2, gy), b2, st, pdl, (size_t)4 * 9 * b2 * sizeof(real_t) + 16);
+	}
+	const dim3 g3((ncols + blk - 1) / blk, gy);
+	const size_t smem = (size_t)2 * 9 * blk * sizeof(real_t);
+	return phase == 1 ? launch_kernel(stream_collide_aa_staged_kernel<real_t, 1>, p, g3, blk, st, pdl, smem)
+	                  : launch_kernel(stream_collide_aa_staged_kernel<real_t, 2>, p, g3, blk, st, pdl, smem);
+}
+#endif
+
 // One pull step src -> src^1 over owned rows [r0,r1): vector kernel for j < NYVECMAX,
 // scalar-order kernel for the ragged tail (LB.c:195-196) or for everything (LB.c:198).
 // jc0 < jc1: restrict the launch to columns [jc0, jc1) (multiples of 8, jc1 may exceed ny and wraps) -- only the
 // in-place vector kernel takes a column range (2-D temporal blocking; needs nyvec == ny)
-int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st, int jc0 = 0, int jc1 = 0)
+// stream_out: in-place kernels store with the evict-first policy (lbm_tuning.hints on the last level of a macro-step)
+int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st, int jc0 = 0, int jc1 = 0, int stream_out = 0)
 {
 	if (r1 <= r0) return LBM_OK;
 	StepParams<real_t> p = make_params(c, src, r0, r1, tail_source);
@@ -383,65 +397,44 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 	}
 	if (c->vw > 1 && c->nyvec > 0) {
 		int V = c->tune.vec;
-		if (c->inplace && src == 0 && c->tune.vec_phase1) V = c->tune.vec_phase1;
 		if (V > c->vw) V = c->vw;
 		unsigned block = (unsigned)c->tune.block;
 		if (c->inplace && sizeof(real_t) == 4 && block > 256) block = 256;      /* launch bounds of the SP in-place kernels */
-		const unsigned long long total = (unsigned long long)rows * (unsigned)(c->nyvec / V);
-		unsigned long long grid = (total + block - 1) / block;
-		if (c->tune.ctas_per_sm > 0) {
-			const unsigned long long cap = (unsigned long long)sm_count(c->cfg.device) * c->tune.ctas_per_sm;
-			if (grid > cap) grid = cap;
-		}
 		/* PDL only where consecutive step kernels follow each other on one stream with nothing between */
 		const int pdl = c->tune.pdl && (c->sync_mode == SYNC_SELF || c->in_wavefront) && c->nyvec == c->ny;
-		cudaError_t e;
+		cudaError_t e = cudaErrorNotYetImplemented;
 		if (c->inplace) {
 			const int phase = src == 0 ? 1 : 2;
-			/* x: the vectors of one row; y: rows, capped (grid-stride) by ctas_per_sm and by the 65535 limit */
-			const unsigned gx = (ncols / (unsigned)V + block - 1) / block;
-			unsigned gy = rows;
-			int pipe = c->tune.rows_per_thread >= 2 && V <= 2;           /* wider vectors: the second register set spills */
-			if (pipe) gy = (rows + (unsigned)c->tune.rows_per_thread - 1) / (unsigned)c->tune.rows_per_thread;
-			else if (c->tune.neighbour == 0) pipe = 2;
-			if (c->tune.ctas_per_sm > 0) {
-				const unsigned cap = (unsigned)(sm_count(c->cfg.device) * c->tune.ctas_per_sm) / gx;
-				if (gy > cap) gy = cap < 1 ? 1 : cap;
-			}
-			if (gy > 65535u) gy = 65535u;
-			const dim3 g2(gx, gy);
-			if (pipe == 1 && V == 1 && c->tune.stage_smem && c->nyvec == c->ny) {   /* next row staged in shared memory by cp.async */
-				const unsigned blk = block > 256 ? 256 : block;
-				const dim3 g3((ncols + blk - 1) / blk, gy);
-				const size_t smem = (size_t)2 * 9 * blk * sizeof(real_t);
-				if (phase == 2 && c->tune.stage_smem == 2 && jc1 <= jc0 && ((size_t)c->ny * sizeof(real_t)) % 16 == 0) {   /* TMA bulk copies both ways; whole rows of 16-byte units only */
-					const unsigned b2 = blk > 128 ? 128 : blk;
-					const dim3 g4(((unsigned)c->ny + b2 - 1) / b2, gy);
-					e = launch_kernel(stream_collide_aa_bulk2_kernel<real_t>, p, g4, b2, st, pdl, (size_t)4 * 9 * b2 * sizeof(real_t) + 16);
-				} else
-				e = phase == 1 ? launch_kernel(stream_collide_aa_staged_kernel<real_t, 1>, p, g3, blk, st, pdl, smem)
-				               : launch_kernel(stream_collide_aa_staged_kernel<real_t, 2>, p, g3, blk, st, pdl, smem);
-			} else
-			switch (V) {
-			case 1: e = launch_aa_v<1>(phase, pipe, p, g2, block, st, pdl); break;
-			case 2: e = launch_aa_v<2>(phase, pipe, p, g2, block, st, pdl); break;
-			case 4: e = launch_aa_v<4>(phase, pipe, p, g2, block, st, pdl); break;
+#ifdef LBM_EXPERIMENTAL
+			e = launch_staged(c, phase, p, rows, ncols, jc1 <= jc0, st, pdl);
+#endif
+			if (e == cudaErrorNotYetImplemented) {
+				/* x: the vectors of one row; y: rows (grid-stride above the 65535 limit) */
+				const dim3 g2((ncols / (unsigned)V + block - 1) / block, rows > 65535u ? 65535u : rows);
+				switch (V) {
+				case 1: e = launch_aa_v<1>(phase, stream_out, p, g2, block, st, pdl); break;
+				case 2: e = launch_aa_v<2>(phase, stream_out, p, g2, block, st, pdl); break;
+				case 4: e = launch_aa_v<4>(phase, stream_out, p, g2, block, st, pdl); break;
 #ifdef LBM_FLOAT
-			case 8: e = launch_aa_v<8>(phase, pipe, p, g2, block, st, pdl); break;
+				case 8: e = launch_aa_v<8>(phase, stream_out, p, g2, block, st, pdl); break;
+#endif
+				default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
+				}
+			}
+		} else {
+			const unsigned long long total = (unsigned long long)rows * (unsigned)(c->nyvec / V);
+			const unsigned grid = (unsigned)((total + block - 1) / block);
+			switch (V) {
+			case 1: e = launch_vec_v<1>(c->tune.hints, p, grid, block, st, pdl); break;
+			case 2: e = launch_vec_v<2>(c->tune.hints, p, grid, block, st, pdl); break;
+			case 4: e = launch_vec_v<4>(c->tune.hints, p, grid, block, st, pdl); break;
+#ifdef LBM_FLOAT
+			case 8: e = launch_vec_v<8>(c->tune.hints, p, grid, block, st, pdl); break;
 #endif
 			default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 			}
-		} else
-		switch (V) {
-		case 1: e = launch_vec_v<1>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
-		case 2: e = launch_vec_v<2>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
-		case 4: e = launch_vec_v<4>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
-#ifdef LBM_FLOAT
-		case 8: e = launch_vec_v<8>(c->tune.neighbour, c->tune.hints, p, (unsigned)grid, block, st, pdl); break;
-#endif
-		default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 		}
-		if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_vec_kernel: %s", cudaGetErrorString(e));
+		if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide kernel: %s", cudaGetErrorString(e));
 		c->launches++;
 		jtail = c->nyvec;
 	}
@@ -460,59 +453,6 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 		c->launches++;
 	}
 	return LBM_OK;
-}
-
-template <int V, int NB>
-int launch_persistent_inst(lbm_ctx *c, const StepParams<real_t> &p, int nsteps, int last_tail, cudaStream_t st)
-{
-	auto kern = stream_collide_persistent_kernel<real_t, V, NB>;
-	const int block = c->tune.block;
-	int occ = 0;
-	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, block, 0));
-	if (c->tune.ctas_per_sm > 0 && occ > c->tune.ctas_per_sm) occ = c->tune.ctas_per_sm;
-	if (occ < 1) return fail(LBM_ERR_CUDA, "persistent kernel does not fit an SM at block %d", block);
-	long long maxgrid = (long long)occ * sm_count(c->cfg.device);
-	if (maxgrid > PROGRESS_SLOTS) maxgrid = PROGRESS_SLOTS;
-	const unsigned long long total = (unsigned long long)c->nxl * (unsigned)(c->nyvec / V);
-	unsigned long long chunk = (total + maxgrid - 1) / maxgrid;
-	chunk = (chunk + 31) / 32 * 32;
-	const unsigned grid = (unsigned)((total + chunk - 1) / chunk);
-	PersistParams q;
-	q.nsteps = nsteps; q.last_tail_source = last_tail; q.chunk = (uint32_t)chunk;
-	q.progress = c->progress; q.abort = c->progress + PROGRESS_SLOTS;
-	q.timeout_ns = 10ull * 1000 * 1000 * 1000;
-	CK(cudaMemsetAsync(c->progress, 0, (PROGRESS_SLOTS + 1) * sizeof(int), st));
-	StepParams<real_t> pp = p;
-	void *args[] = {(void *)&pp, (void *)&q};
-	CK(cudaLaunchCooperativeKernel((const void *)kern, dim3(grid), dim3(block), args, 0, st));
-	c->launches++;
-	c->launches_persistent = 1;
-	return LBM_OK;
-}
-
-// nsteps lattice steps starting from buffer `src` in ONE cooperative launch (single-slab contexts
-// whose rows are all vector columns); tail source on every step but the last unless last_tail
-int launch_persistent(lbm_ctx *c, int src, int nsteps, int last_tail, cudaStream_t st)
-{
-	StepParams<real_t> p = make_params(c, src, 0, c->nxl, 1);
-	int V = c->tune.vec;
-	if (V > c->vw) V = c->vw;
-	const int nb = c->tune.neighbour;
-	switch (V) {
-	case 1: return launch_persistent_inst<1, 1>(c, p, nsteps, last_tail, st);
-	case 2: return nb ? launch_persistent_inst<2, 1>(c, p, nsteps, last_tail, st) : launch_persistent_inst<2, 0>(c, p, nsteps, last_tail, st);
-	case 4: return nb ? launch_persistent_inst<4, 1>(c, p, nsteps, last_tail, st) : launch_persistent_inst<4, 0>(c, p, nsteps, last_tail, st);
-#ifdef LBM_FLOAT
-	case 8: return nb ? launch_persistent_inst<8, 1>(c, p, nsteps, last_tail, st) : launch_persistent_inst<8, 0>(c, p, nsteps, last_tail, st);
-#endif
-	}
-	return fail(LBM_ERR_ARG, "launch_persistent: vec %d", V);
-}
-
-bool use_persistent(const lbm_ctx *c)
-{
-	if (c->sync_mode != SYNC_SELF || c->vw <= 1 || c->nyvec != c->ny || c->inplace) return false;
-	return c->tune.persistent != 0;
 }
 
 int launch_source(lbm_ctx *c, int buf, cudaStream_t st)
@@ -708,7 +648,7 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 		const int tail = t0 + s != nsteps - 1;
 		if (!(flags && seam)) {
 			chain_open = false;
-			return launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[0], j0, j1);
+			return launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[0], j0, j1, c->tune.hints && s == kk - 1);
 		}
 		if (!chain_open) {
 			if ((ce = cudaEventRecord(c->ev_main, c->stream[0])) != cudaSuccess) return (int)LBM_ERR_CUDA;
@@ -716,7 +656,7 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 			chain_open = true;
 		}
 		if ((r = launch_wait(c, c->stream[1]))) return r;
-		if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[1], j0, j1))) return r;
+		if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[1], j0, j1, c->tune.hints && s == kk - 1))) return r;
 		return launch_signal(c, c->stream[1]);
 	});
 	if (ce != cudaSuccess) return fail(LBM_ERR_CUDA, "enqueue_macro: %s", cudaGetErrorString(ce));
@@ -724,195 +664,6 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 	if (flags) {
 		CK(cudaEventRecord(c->ev_bnd[0], c->stream[1]));
 		CK(cudaStreamWaitEvent(c->stream[0], c->ev_bnd[0], 0));
-	}
-	return LBM_OK;
-}
-
-/* ---- fused pairs: phase 2 of step t and phase 1 of step t+1 in one pass (lbm_tuning.fuse_rows) ---- */
-template <typename K, typename A, typename B>
-cudaError_t launch_kernel2(K kern, const A &a, const B &b, dim3 grid, unsigned block, cudaStream_t st, int pdl)
-{
-	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-	cudaLaunchAttribute at[1];
-	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-	at[0].val.programmaticStreamSerializationAllowed = 1;
-	cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-	return cudaLaunchKernelEx(&cfg, kern, a, b);
-}
-
-bool pairs_ok(const lbm_ctx *c)
-{
-	return c->inplace && c->sync_mode == SYNC_SELF && c->tune.fuse_rows >= 3 && c->vw > 1 && c->nyvec == c->ny;
-}
-
-/* rows [r0, r1): phase 2 (tail1) of every site + phase 1 (tail2) of the tile interiors, then phase 1 of the tile rims */
-int launch_pair(lbm_ctx *c, int r0, int r1, int tail1, int tail2, cudaStream_t st)
-{
-	StepParams<real_t> p = make_params(c, 1, r0, r1, tail1);
-	const int tr = c->tune.fuse_rows;
-	const int tc = c->tune.block == 64 ? 64 : 128;
-	PairParams q;
-	q.tile_rows = tr; q.tail_source2 = tail2;
-	const unsigned row_tiles = (unsigned)((r1 - r0 + tr - 1) / tr), col_tiles = (unsigned)((c->ny + tc - 1) / tc);
-	if (row_tiles > 65535u) return fail(LBM_ERR_ARG, "fuse_rows %d: %u row tiles", tr, row_tiles);
-	cudaError_t e = tc == 64 ? launch_kernel2(stream_collide_aa_pair_kernel<real_t, 64>, p, q, dim3(col_tiles, row_tiles), 64, st, c->tune.pdl)
-	                         : launch_kernel2(stream_collide_aa_pair_kernel<real_t, 128>, p, q, dim3(col_tiles, row_tiles), 128, st, c->tune.pdl);
-	if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_aa_pair_kernel: %s", cudaGetErrorString(e));
-	StepParams<real_t> pe = make_params(c, 0, r0, r1, tail2);
-	EdgeParams qe;
-	qe.tile_rows = tr; qe.tile_cols = tc; qe.edge_rows = 2 * (int)row_tiles; qe.col_tiles = (int)col_tiles;
-	const unsigned gy = (unsigned)qe.edge_rows + (unsigned)(r1 - r0);
-	if (gy > 65535u) return fail(LBM_ERR_ARG, "fuse_rows %d: %u edge launch rows", tr, gy);
-	const unsigned need = (unsigned)c->ny > 2 * col_tiles ? (unsigned)c->ny : 2 * col_tiles;
-	e = launch_kernel2(stream_collide_aa_edges_kernel<real_t>, pe, qe, dim3((need + 127) / 128, gy), 128, st, c->tune.pdl);
-	if (e != cudaSuccess) return fail(LBM_ERR_CUDA, "stream_collide_aa_edges_kernel: %s", cudaGetErrorString(e));
-	c->launches += 2;
-	return LBM_OK;
-}
-
-/* nsteps (even) as: phase 1 | (phase 2 + phase 1) x (nsteps/2 - 1) | phase 2 */
-int run_pairs(lbm_ctx *c, int nsteps)
-{
-	int rc;
-	struct Scope { lbm_ctx *c; Scope(lbm_ctx *c_) : c(c_) { c->in_wavefront = 1; } ~Scope() { c->in_wavefront = 0; } } scope(c);
-	cudaStream_t st = c->stream[0];
-	if ((rc = launch_step(c, 0, 0, c->nxl, 1, st))) return rc;
-	for (int t = 1; t + 1 < nsteps; t += 2)
-		if ((rc = launch_pair(c, 0, c->nxl, 1, 1, st))) return rc;
-	return launch_step(c, 1, 0, c->nxl, 0, st);
-}
-
-/* ---- dataflow kernel: a whole macro-step in one launch (single slab, whole-row pieces) ---- */
-/* Its item order: tb_for_each_launch's, except that inverted-pyramid level s is issued right after level s-1 of the
- * last other row piece instead of after all of that piece's levels.  Valid: inverted level s reads rows
- * [nx-s-1, nx+s+1) of level s-1, which lie in that piece's, the pyramid's and its own level s-1 -- all issued
- * earlier.  The short ring-closing levels then run beside the big launches instead of as a serial chain at the end. */
-bool df_plan_ok(const TbPlan &pl)
-{
-	return pl.k >= 2 && pl.cols.npieces == 1 && pl.cols.piece[0].type == TB_WHOLE && pl.rows.piece[0].type != TB_WHOLE;
-}
-
-template <typename F> int df_for_each_launch(const TbPlan &pl, int kk, F visit)
-{
-	const int np = pl.rows.npieces;
-	const int inv = (np >= 2 && pl.rows.piece[np - 1].type == TB_INVERTED) ? np - 1 : -1;
-	int rc, r0, r1;
-	for (int ri = 0; ri < np; ri++) {
-		if (ri == inv) continue;
-		const bool carries_inv = inv >= 0 && ri == inv - 1;
-		for (int s = 0; s < kk; s++) {
-			if (carries_inv) {
-				tb_range(pl.rows, pl.rows.piece[inv], s, &r0, &r1);
-				if (r1 > r0 && (rc = visit(s, r0, r1))) return rc;
-			}
-			tb_range(pl.rows, pl.rows.piece[ri], s, &r0, &r1);
-			if (r1 > r0 && (rc = visit(s, r0, r1))) return rc;
-		}
-	}
-	return 0;
-}
-
-/* device copy of the launch list of one macro-step of kk levels starting at timestep t0 (slot 0: cached full macro-step) */
-int df_upload_list(lbm_ctx *c, int slot, const TbPlan &pl, int kk, int t0, int nsteps, int chunks, int *nlaunch, unsigned *nitems)
-{
-	std::vector<DfLaunch> l;
-	unsigned long long first = 0;
-	df_for_each_launch(pl, kk, [&](int s, int r0, int r1) {
-		DfLaunch d;
-		d.level = s; d.r0 = r0 >= c->nxl ? r0 - c->nxl : r0; d.rows = r1 - r0;
-		d.tail_source = t0 + s != nsteps - 1;
-		d.first = (unsigned)first;
-		first += (unsigned long long)d.rows * (unsigned)chunks;
-		l.push_back(d);
-		return 0;
-	});
-	if (first >= (1ull << 31)) return fail(LBM_ERR_ARG, "dataflow: %llu items in a macro-step", first);
-	if (l.size() > c->df_list_cap[slot]) {
-		if (c->df_list[slot]) CK(cudaFree(c->df_list[slot]));
-		c->df_list[slot] = nullptr; c->df_list_cap[slot] = 0;
-		CK(cudaMalloc(&c->df_list[slot], l.size() * sizeof(DfLaunch)));
-		c->df_list_cap[slot] = l.size();
-	}
-	CK(cudaMemcpyAsync(c->df_list[slot], l.data(), l.size() * sizeof(DfLaunch), cudaMemcpyHostToDevice, c->stream[0]));   /* pageable: staged before return */
-	*nlaunch = (int)l.size(); *nitems = (unsigned)first;
-	return LBM_OK;
-}
-
-template <int V>
-int launch_dataflow_v(lbm_ctx *c, const StepParams<real_t> &p, const DfParams &q, unsigned block, cudaStream_t st)
-{
-	const void *kern = c->tune.hints ? (const void *)stream_collide_aa_dataflow_kernel<real_t, V, false>
-	                                 : (const void *)stream_collide_aa_dataflow_kernel<real_t, V, true>;
-	int occ = 0;
-	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, (int)block, 0));
-	if (c->tune.ctas_per_sm > 0 && occ > c->tune.ctas_per_sm) occ = c->tune.ctas_per_sm;
-	if (occ < 1) return fail(LBM_ERR_CUDA, "dataflow kernel does not fit an SM at block %u", block);
-	unsigned long long grid = (unsigned long long)occ * sm_count(c->cfg.device);
-	if (grid > q.nitems) grid = q.nitems;
-	StepParams<real_t> pp = p;
-	DfParams qq = q;
-	void *args[] = {(void *)&pp, (void *)&qq};
-	CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(block), args, 0, st));
-	c->launches++;
-	return LBM_OK;
-}
-
-int launch_dataflow(lbm_ctx *c, int slot, int nlaunch, unsigned nitems, int levels, int chunks, int iters, unsigned block, cudaStream_t st)
-{
-	StepParams<real_t> p = make_params(c, 0, 0, c->nxl, 1);
-	DfParams q;
-	q.list = c->df_list[slot]; q.nlaunch = nlaunch; q.nitems = nitems; q.chunks = chunks; q.iters = iters;
-	q.cnt = c->df_cnt; q.levels = levels;
-	q.abort = c->progress + PROGRESS_SLOTS;
-	q.timeout_ns = 10ull * 1000 * 1000 * 1000;
-	CK(cudaMemsetAsync(c->df_cnt, 0, (size_t)levels * c->nxl * sizeof(int), st));
-	c->launches_persistent = 1;                                  /* lbm_sync then looks at the abort word */
-	int V = c->tune.vec;
-	if (V > c->vw) V = c->vw;
-	switch (V) {
-	case 1: return launch_dataflow_v<1>(c, p, q, block, st);
-	case 2: return launch_dataflow_v<2>(c, p, q, block, st);
-	case 4: return launch_dataflow_v<4>(c, p, q, block, st);
-#ifdef LBM_FLOAT
-	case 8: return launch_dataflow_v<8>(c, p, q, block, st);
-#endif
-	}
-	return fail(LBM_ERR_ARG, "launch_dataflow: vec %d", V);
-}
-
-int run_dataflow(lbm_ctx *c, int nsteps, const TbPlan &pl)
-{
-	int rc;
-	const int k = pl.k;
-	int V = c->tune.vec;
-	if (V > c->vw) V = c->vw;
-	unsigned block = (unsigned)c->tune.block;
-	if (block > (sizeof(real_t) == 4 ? 256u : 128u)) block = sizeof(real_t) == 4 ? 256u : 128u;    /* launch bounds of the kernel */
-	const int iters = c->tune.dataflow;
-	const unsigned cw = block * (unsigned)iters;                 /* vectors per chunk */
-	const int chunks = (int)(((unsigned)(c->ny / V) + cw - 1) / cw);
-	const size_t need = (size_t)k * c->nxl;
-	if (need > c->df_cnt_ints) {
-		if (c->df_cnt) CK(cudaFree(c->df_cnt));
-		c->df_cnt = nullptr; c->df_cnt_ints = 0;
-		CK(cudaMalloc(&c->df_cnt, need * sizeof(int)));
-		c->df_cnt_ints = need;
-	}
-	CK(cudaMemsetAsync(c->progress + PROGRESS_SLOTS, 0, sizeof(int), c->stream[0]));
-	int t = 0;
-	if (nsteps - k >= k) {                                       /* full macro-steps, every level with its tail source */
-		if (!c->df_nlaunch && (rc = df_upload_list(c, 0, pl, k, 0, 1 << 30, chunks, &c->df_nlaunch, &c->df_nitems))) return rc;
-		for (; nsteps - k - t >= k; t += k)
-			if ((rc = launch_dataflow(c, 0, c->df_nlaunch, c->df_nitems, k, chunks, iters, block, c->stream[0]))) return rc;
-	}
-	while (t < nsteps) {                                         /* the last one or two: the run's last level leaves A un-sourced */
-		const int kk = nsteps - t < k ? nsteps - t : k;
-		int nl = 0;
-		unsigned ni = 0;
-		if ((rc = df_upload_list(c, 1, pl, kk, t, nsteps, chunks, &nl, &ni))) return rc;
-		if ((rc = launch_dataflow(c, 1, nl, ni, kk, chunks, iters, block, c->stream[0]))) return rc;
-		t += kk;
 	}
 	return LBM_OK;
 }
@@ -929,7 +680,6 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 			if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
 		return LBM_OK;
 	}
-	if (c->tune.dataflow > 0 && c->sync_mode == SYNC_SELF && c->vw > 1 && c->nyvec == c->ny && df_plan_ok(pl)) return run_dataflow(c, nsteps, pl);
 	int t = 0;
 	struct Scope { lbm_ctx *c; Scope(lbm_ctx *c_) : c(c_) { c->in_wavefront = 1; } ~Scope() { c->in_wavefront = 0; } } scope(c);
 	if (c->tune.graph > 0 && nsteps - k >= k && c->sync_mode == SYNC_SELF) {      /* slabs: the epochs of wait/signal change per launch */
@@ -991,8 +741,11 @@ int lbm_initialize_arrays(lbm_ctx *c, const lbm_scene *scene)
 	sc.disc_r2 = scene->disc_r < 0 ? -1 : scene->disc_r * scene->disc_r;
 	cudaStream_t st = c->stream[0];
 	const size_t nwords = (size_t)c->nxl * c->ldw, nsites = (size_t)c->nxl * c->ny;
-	scene_mask_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(c->mask, sc, c->cfg.row_lo, c->nxl, c->ny, c->ldw);
+	if (scene->channel_walls < 0 || scene->channel_walls > 2) return fail(LBM_ERR_ARG, "lbm_initialize_arrays: channel_walls %d not in {0,1,2}", scene->channel_walls);
+	scene_mask_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(c->mask, c->slip, sc, c->cfg.row_lo, c->nxl, c->ny, c->ldw);
 	CK(cudaGetLastError());
+	c->has_slip = scene->channel_walls == 2;
+	drop_graph(c);                                               /* captured launches carry the slip pointer */
 	/* INITIALDENSITY * OMEGA_s in real_t (LB.c:583-591) */
 	scene_fill_kernel<real_t><<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(
 		c->f[0], c->f[1] /* nullptr when in place */, c->plane, c->ldy, c->nxl, c->ny, c->cfg.row_lo, scene->rho0, c->w0, c->w14, c->w58,
@@ -1000,6 +753,33 @@ int lbm_initialize_arrays(lbm_ctx *c, const lbm_scene *scene)
 	CK(cudaGetLastError());
 	c->launches += 2;
 	c->has_state = 1;
+	return LBM_OK;
+}
+
+/* walls: chars (0 fluid, 1 bounce-back, 2 / 3 reflect with normal x / y) -> device scratch -> packed bit planes.
+ * The slab's first row is host row `first`; row stride ldy.  Synchronous (the values are checked). */
+static int set_walls_impl(lbm_ctx *c, const char *walls, int ldy, int first)
+{
+	cudaStream_t st = c->stream[0];
+	char *dwalls = nullptr;
+	int *dflags = nullptr;
+	const size_t ldc = (size_t)c->ny;
+	CK(cudaMallocAsync(&dwalls, (size_t)c->nxl * ldc, st));
+	CK(cudaMallocAsync(&dflags, 2 * sizeof(int), st));
+	CK(cudaMemsetAsync(dflags, 0, 2 * sizeof(int), st));
+	CK(cudaMemcpy2DAsync(dwalls, ldc, walls + (size_t)first * ldy, (size_t)ldy, (size_t)c->ny, (size_t)c->nxl, cudaMemcpyHostToDevice, st));
+	const size_t nwords = (size_t)c->nxl * c->ldw;
+	mask_pack_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(dwalls, ldc, c->mask, c->slip, c->nxl, c->ny, c->ldw, dflags);
+	CK(cudaGetLastError());
+	c->launches++;
+	int fl[2] = {0, 0};
+	CK(cudaMemcpyAsync(fl, dflags, sizeof fl, cudaMemcpyDeviceToHost, st));
+	CK(cudaFreeAsync(dwalls, st));
+	CK(cudaFreeAsync(dflags, st));
+	CK(cudaStreamSynchronize(st));
+	if (fl[0]) return fail(LBM_ERR_ARG, "walls must hold 0 (fluid), 1 (bounce-back: LB.c:246 tests == 1, LB.c:455 tests == 0), 2 or 3 (reflect, normal x / y)");
+	c->has_slip = fl[1] != 0;
+	drop_graph(c);
 	return LBM_OK;
 }
 
@@ -1025,24 +805,7 @@ static int upload_impl(lbm_ctx *c, const real_t *fA, const real_t *fB, const cha
 			                     src + s * hplane + row0, (size_t)ldy * sizeof(real_t),
 			                     (size_t)c->ny * sizeof(real_t), (size_t)c->nxl, cudaMemcpyHostToDevice, st));
 	}
-	/* walls: chars -> device scratch -> packed bits */
-	char *dwalls = nullptr;
-	int *dbad = nullptr;
-	const size_t ldc = (size_t)c->ny;
-	CK(cudaMallocAsync(&dwalls, (size_t)c->nxl * ldc, st));
-	CK(cudaMallocAsync(&dbad, sizeof(int), st));
-	CK(cudaMemsetAsync(dbad, 0, sizeof(int), st));
-	CK(cudaMemcpy2DAsync(dwalls, ldc, walls + row0, (size_t)ldy, (size_t)c->ny, (size_t)c->nxl, cudaMemcpyHostToDevice, st));
-	const size_t nwords = (size_t)c->nxl * c->ldw;
-	mask_pack_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(dwalls, ldc, c->mask, c->nxl, c->ny, c->ldw, dbad);
-	CK(cudaGetLastError());
-	c->launches++;
-	int bad = 0;
-	CK(cudaMemcpyAsync(&bad, dbad, sizeof(int), cudaMemcpyDeviceToHost, st));
-	CK(cudaFreeAsync(dwalls, st));
-	CK(cudaFreeAsync(dbad, st));
-	CK(cudaStreamSynchronize(st));
-	if (bad) return fail(LBM_ERR_ARG, "lbm_upload: walls must hold 0 or 1 (LB.c:246 tests == 1, LB.c:455 tests == 0)");
+	if ((rc = set_walls_impl(c, walls, ldy, first))) return rc;
 	c->has_state = 1;
 	return LBM_OK;
 }
@@ -1057,6 +820,49 @@ int lbm_upload_slab(lbm_ctx *c, const real_t *fA, const real_t *fB, const char *
 {
 	if (!c) return fail(LBM_ERR_ARG, "lbm_upload_slab: null ctx");
 	return upload_impl(c, fA, fB, walls, ldy, c->nxl, 0);
+}
+
+int lbm_set_walls(lbm_ctx *c, const char *walls, int ldy)
+{
+	if (!c || !walls) return fail(LBM_ERR_ARG, "lbm_set_walls: null argument");
+	if (ldy < c->ny) return fail(LBM_ERR_ARG, "lbm_set_walls: ldy %d < ny %d", ldy, c->ny);
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;
+	return set_walls_impl(c, walls, ldy, c->cfg.row_lo);
+}
+
+/* Geometry from a file instead of the hard-wired barrier of LB.c:567-578: text, one lattice row per line, NY entries
+ * per line, each one of the digits 0 1 2 3, optionally separated by blanks and/or commas (so both "0100" and the
+ * "0, 1, 0, 0" style of the reference's own data/<step>.csv dumps parse); lines starting with '#' are comments. */
+int lbm_load_walls(lbm_ctx *c, const char *path)
+{
+	if (!c || !path) return fail(LBM_ERR_ARG, "lbm_load_walls: null argument");
+	FILE *fp = fopen(path, "r");
+	if (!fp) return fail(LBM_ERR_IO, "Error opening file %s", path);
+	const int nx = c->cfg.nx, ny = c->ny;
+	std::vector<char> walls((size_t)nx * ny);
+	int row = 0, col = 0, ch, rc = LBM_OK;
+	bool comment = false, line_start = true;
+	while (rc == LBM_OK && (ch = fgetc(fp)) != EOF) {
+		if (comment) { if (ch == '\n') { comment = false; line_start = true; } continue; }
+		if (ch == '#' && line_start) { comment = true; continue; }
+		if (ch == '\n') {
+			if (col == 0) { line_start = true; continue; }                         /* blank line */
+			if (col != ny) rc = fail(LBM_ERR_IO, "%s: row %d has %d entries, the lattice has %d columns", path, row, col, ny);
+			row++; col = 0; line_start = true;
+			continue;
+		}
+		line_start = false;
+		if (ch == ' ' || ch == '\t' || ch == ',' || ch == '\r') continue;
+		if (ch < '0' || ch > '3') { rc = fail(LBM_ERR_IO, "%s: row %d: unexpected character '%c' (entries are 0, 1, 2 or 3)", path, row, ch); break; }
+		if (row >= nx || col >= ny) { rc = fail(LBM_ERR_IO, "%s: more than %d rows of %d entries", path, nx, ny); break; }
+		walls[(size_t)row * ny + col++] = (char)(ch - '0');
+	}
+	fclose(fp);
+	if (rc != LBM_OK) return rc;
+	if (col == ny) { row++; col = 0; }                                              /* last line without a newline */
+	if (col != 0 || row != nx) return fail(LBM_ERR_IO, "%s: %d complete rows, the lattice has %d", path, row, nx);
+	return lbm_set_walls(c, walls.data(), ny);
 }
 
 static int download_impl(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, int ldy, int host_rows, int first)
@@ -1080,7 +886,7 @@ static int download_impl(lbm_ctx *c, real_t *fA, real_t *fB, char *walls_out, in
 		char *dwalls = nullptr;
 		const size_t ldc = (size_t)c->ny, nsites = (size_t)c->nxl * c->ny;
 		CK(cudaMallocAsync(&dwalls, nsites, st));
-		mask_unpack_kernel<<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(c->mask, dwalls, ldc, c->nxl, c->ny, c->ldw);
+		mask_unpack_kernel<<<(unsigned)((nsites + 255) / 256), 256, 0, st>>>(c->mask, c->has_slip ? c->slip : nullptr, dwalls, ldc, c->nxl, c->ny, c->ldw);
 		CK(cudaGetLastError());
 		c->launches++;
 		CK(cudaMemcpy2DAsync(walls_out + row0, (size_t)ldy, dwalls, ldc, (size_t)c->ny, (size_t)c->nxl, cudaMemcpyDeviceToHost, st));
@@ -1130,11 +936,6 @@ int lbm_sync(lbm_ctx *c)
 	if ((rc = set_device(c))) return rc;
 	CK(cudaStreamSynchronize(c->stream[1]));
 	CK(cudaStreamSynchronize(c->stream[0]));
-	if (c->sync_mode == SYNC_SELF && c->launches_persistent) {
-		int ab = 0;
-		CK(cudaMemcpy(&ab, c->progress + PROGRESS_SLOTS, sizeof ab, cudaMemcpyDeviceToHost));
-		if (ab) return fail(LBM_ERR_STATE, "persistent / dataflow kernel: a dependency wait timed out");
-	}
 	if (c->sync_mode == SYNC_FLAGS) {
 		int fl[4];
 		CK(cudaMemcpy(fl, c->flags, sizeof fl, cudaMemcpyDeviceToHost));
@@ -1154,8 +955,6 @@ int lbm_run(lbm_ctx *c, int nsteps)
 	/* Source(A) of the first step; every later Source is fused into the tail of the step
 	 * before it, the last step leaves A un-sourced as the reference does (LB.c:192-205). */
 	if ((rc = enqueue_prologue(c, LBM_BUF_A))) return rc;
-	if (use_persistent(c)) return launch_persistent(c, LBM_BUF_A, nsteps, 0, c->stream[0]);
-	if (pairs_ok(c)) return run_pairs(c, nsteps);
 	if (c->inplace && (c->sync_mode == SYNC_SELF || c->sync_mode == SYNC_FLAGS) && c->tune.tb_depth >= 2) return run_wavefront(c, nsteps);
 	int t = 0;
 	if (c->tune.graph > 0 && c->sync_mode == SYNC_SELF) {
@@ -1307,15 +1106,13 @@ int lbm_macroscopic(lbm_ctx *c, real_t *rho, real_t *ux, real_t *uy)
 	return LBM_OK;
 }
 
-int lbm_print_lattice(lbm_ctx *c, const char *path)
+/* the rows of one slab, appended to an open file: PrintLattice's loop body (LB.c:618-637) */
+static int print_rows(lbm_ctx *c, FILE *fp)
 {
-	if (!c || !path) return fail(LBM_ERR_ARG, "lbm_print_lattice: null argument");
 	const size_t n = (size_t)c->nxl * c->ny;
 	std::vector<real_t> ux(n), uy(n);
 	int rc;
 	if ((rc = lbm_macroscopic(c, nullptr, ux.data(), uy.data()))) return rc;
-	FILE *fp = fopen(path, "w");
-	if (!fp) return fail(LBM_ERR_IO, "Error opening file %s", path);       /* LB.c:616 */
 	std::vector<char> line((size_t)c->ny * 400 + 8);                       /* "%.10lf" of DBL_MAX is 320 characters (a diverged run) */
 	for (int i = 0; i < c->nxl; i++) {
 		size_t pos = 0;
@@ -1326,10 +1123,36 @@ int lbm_print_lattice(lbm_ctx *c, const char *path)
 			if (j < c->ny - 1) { line[pos++] = ','; line[pos++] = ' '; }     /* LB.c:634 */
 		}
 		line[pos++] = '\n';
-		fwrite(line.data(), 1, pos, fp);
+		if (fwrite(line.data(), 1, pos, fp) != pos) return fail(LBM_ERR_IO, "PrintLattice: short write");
 	}
-	fclose(fp);
 	return LBM_OK;
+}
+
+int lbm_print_lattice_group(lbm_ctx **slabs, int n, const char *path)
+{
+	if (!slabs || n < 1 || !path) return fail(LBM_ERR_ARG, "lbm_print_lattice_group: bad argument");
+	int next = 0;
+	for (int k = 0; k < n; k++) {                                          /* one file = the whole lattice, rows in order */
+		if (!slabs[k] || slabs[k]->cfg.row_lo != next) return fail(LBM_ERR_ARG, "lbm_print_lattice_group: slab %d does not continue at row %d", k, next);
+		next = slabs[k]->cfg.row_hi;
+	}
+	if (next != slabs[0]->cfg.nx) return fail(LBM_ERR_ARG, "lbm_print_lattice_group: the slabs cover rows [0,%d) of %d", next, slabs[0]->cfg.nx);
+	FILE *fp = fopen(path, "w");
+	if (!fp) return fail(LBM_ERR_IO, "Error opening file %s", path);       /* LB.c:616 */
+	int rc = LBM_OK;
+	for (int k = 0; k < n && rc == LBM_OK; k++) rc = print_rows(slabs[k], fp);
+	fclose(fp);
+	return rc;
+}
+
+int lbm_print_lattice(lbm_ctx *c, const char *path)
+{
+	if (!c || !path) return fail(LBM_ERR_ARG, "lbm_print_lattice: null argument");
+	FILE *fp = fopen(path, "w");
+	if (!fp) return fail(LBM_ERR_IO, "Error opening file %s", path);       /* LB.c:616 */
+	const int rc = print_rows(c, fp);
+	fclose(fp);
+	return rc;
 }
 
 static int reduce_u64(lbm_ctx *c, int buf, int what, unsigned long long *out)
@@ -1384,26 +1207,27 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	const int vmax = 32 / (int)sizeof(real_t);
 	if ((n.vec != 1 && n.vec != 2 && n.vec != 4 && n.vec != 8) || n.vec > vmax) return fail(LBM_ERR_ARG, "lbm_set_tuning: vec %d", n.vec);
 	if (n.block < 32 || n.block > 512 || (n.block & 31)) return fail(LBM_ERR_ARG, "lbm_set_tuning: block %d", n.block);
-	if (n.neighbour < 0 || n.neighbour > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: neighbour %d", n.neighbour);
 	if (n.hints < 0 || n.hints > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
-	if (n.ctas_per_sm < 0 || n.ctas_per_sm > 32) return fail(LBM_ERR_ARG, "lbm_set_tuning: ctas_per_sm %d", n.ctas_per_sm);
-	if (n.persistent < 0 || n.persistent > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: persistent %d", n.persistent);
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
 	if (n.tb_rows < 0 || n.tb_cols < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d, tb_cols %d", n.tb_rows, n.tb_cols);
-	if (n.vec_phase1 != 0 && ((n.vec_phase1 != 1 && n.vec_phase1 != 2 && n.vec_phase1 != 4 && n.vec_phase1 != 8) || n.vec_phase1 > vmax))
-		return fail(LBM_ERR_ARG, "lbm_set_tuning: vec_phase1 %d", n.vec_phase1);
-	if (n.rows_per_thread < 0 || n.rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_tuning: rows_per_thread %d", n.rows_per_thread);
-	if (n.fuse_rows < 0 || (n.fuse_rows > 0 && n.fuse_rows < 3) || n.fuse_rows > 4096) return fail(LBM_ERR_ARG, "lbm_set_tuning: fuse_rows %d (0 or 3..4096)", n.fuse_rows);
-	if (n.stage_smem < 0 || n.stage_smem > 2) return fail(LBM_ERR_ARG, "lbm_set_tuning: stage_smem %d", n.stage_smem);
-	if (n.dataflow < 0 || n.dataflow > 64) return fail(LBM_ERR_ARG, "lbm_set_tuning: dataflow %d (0..64)", n.dataflow);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
 	                                                           "the A/B buffers have write-after-read hazards between bands");
 	drop_graph(c);
 	c->tune = n;
 	return LBM_OK;
 }
+#ifdef LBM_EXPERIMENTAL
+int lbm_set_experimental(lbm_ctx *c, const lbm_experimental *x)
+{
+	if (!c || !x) return fail(LBM_ERR_ARG, "lbm_set_experimental: null argument");
+	if (x->stage_smem < 0 || x->stage_smem > 2 || x->rows_per_thread < 0 || x->rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_experimental: stage_smem %d, rows_per_thread %d", x->stage_smem, x->rows_per_thread);
+	drop_graph(c);
+	c->exp = *x;
+	return LBM_OK;
+}
+#endif
 int lbm_get_tuning(lbm_ctx *c, lbm_tuning *t)
 {
 	if (!c || !t) return fail(LBM_ERR_ARG, "lbm_get_tuning: null argument");
@@ -1418,20 +1242,11 @@ int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb
 	const int per128 = 128 / (int)sizeof(real_t);
 	const int ldy = ((ny + per128 - 1) / per128) * per128;
 	static thread_local TbPlan pl;
-	if (multi < 0 || multi > 2) { fail(LBM_ERR_ARG, "lbm_tb_schedule: multi %d", multi); return -1; }
+	if (multi < 0 || multi > 1) { fail(LBM_ERR_ARG, "lbm_tb_schedule: multi %d", multi); return -1; }
 	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi == 1, tb_depth, tb_rows, tb_cols);
 	if (depth_used) *depth_used = pl.k;
 	if (pl.k < 2) return 0;
 	int n = 0;
-	if (multi == 2) {                                            /* item order of the dataflow kernel */
-		if (!df_plan_ok(pl)) { fail(LBM_ERR_ARG, "lbm_tb_schedule: the dataflow kernel takes full-width row bands only"); return -1; }
-		df_for_each_launch(pl, pl.k, [&](int s, int r0, int r1) {
-			if (n < cap) { int *o = launches + 6 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = o[4] = o[5] = 0; }
-			n++;
-			return 0;
-		});
-		return n;
-	}
 	tb_for_each_launch(pl, pl.k, [&](int s, int r0, int r1, int j0, int j1, int seam) {
 		if (n < cap) { int *o = launches + 6 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; o[5] = seam; }
 		n++;
@@ -1567,7 +1382,7 @@ static int group_run_wavefront(lbm_ctx **slabs, int n, int nsteps)
 						tb_range(cols, cols.piece[ci], s, &j0, &j1);
 						if (r1 <= r0 || j1 <= j0) continue;
 						if (cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
-						if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1))) return rc;
+						if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1, c->tune.hints && s == kk - 1))) return rc;
 					}
 				}
 				CK(cudaEventRecord(c->ev_main, c->stream[0]));
@@ -1587,7 +1402,7 @@ static int group_run_wavefront(lbm_ctx **slabs, int n, int nsteps)
 					if ((rc = set_device(c))) return rc;
 					CK(cudaStreamWaitEvent(c->stream[1], up->ev_bnd[prev], 0));
 					CK(cudaStreamWaitEvent(c->stream[1], dn->ev_bnd[prev], 0));
-					if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[1], j0, j1))) return rc;
+					if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[1], j0, j1, c->tune.hints && s == kk - 1))) return rc;
 				}
 				for (int p = 0; p < n; p++) {
 					lbm_ctx *c = slabs[p];

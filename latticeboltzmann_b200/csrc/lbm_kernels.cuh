@@ -5,11 +5,12 @@
 // it computes it is B200-first:
 //   * one fused pull kernel: stream + collide + bounce-back + body force of the
 //     NEXT step + halo push, A/B double buffer, SoA f[s][row][j] planes;
-//   * each thread owns V consecutive sites of one row (128-bit aligned vector
-//     loads/stores along j); the +-1 column neighbours of the six shifted
-//     streams come from the adjacent lane by warp shuffle, so every element of
-//     f is fetched from memory exactly once per step (144 B DP / 72 B SP per
-//     site update);
+//   * each thread owns V consecutive sites of one row (aligned vector loads /
+//     stores along j); the +-1 column element of the six shifted streams is one
+//     extra element load that hits the line a neighbouring lane fetches anyway
+//     (coalesced in L1), so HBM sees every element of f once per step (144 B DP /
+//     72 B SP per site update) -- measured equal or faster than exchanging it by
+//     warp shuffle (profiles/r01_run2, r01_run17);
 //   * walls are a packed bitmask (1 bit/site); x-periodicity and the multi-GPU
 //     slab decomposition are the same mechanism: every slab carries two halo
 //     rows, and the threads of the first/last owned row store the three speeds
@@ -58,6 +59,9 @@ template <typename T> struct StepParams {
 	int r0, r1;            // owned-row range of this launch
 	int vw;                // VECWIDTH of the reference build being matched
 	int tail_source;       // apply the NEXT step's ApplySource to column 0 before storing
+	int outflow;           // 0: y wraps periodically (WRAPAROUND 1, LB.c:42-43,233-234); 1: open ends, see pull_columns()
+	const uint32_t *slip;  // nullptr: every wall site bounces back (LB.c:246-255); else two bit planes [2][nxl][ldw]:
+	                       // plane 0 = "reflect" (slip, LB.c:21) walls whose normal is x, plane 1 = normal y
 	T w0, w14, w58;        // OMEGA0/14/58 (LB.c:38-40), formed on the host in T
 	T itau;                // REAL_T(1.0)/TAU (LB.c:323)
 	double itau_d;         // (1.0/TAU) in double (LB.c:295,456)
@@ -260,6 +264,28 @@ template <typename T> __device__ __forceinline__ void bounce(const T (&f)[9], T 
 	for (int s = 1; s < 9; s++) o[s] = f[opposite(s)];
 }
 
+// "reflect" (slip) walls, named at LB.c:21 but not implemented by the reference: specular reflection instead of
+// reversal.  NORMAL_X: the wall's normal is the x (row) axis -- the channel walls -- so (dx,dy) leaves as (-dx,dy);
+// otherwise the normal is y and (dx,dy) leaves as (dx,-dy).  Like bounce-back a permutation of the site's own nine
+// values (in-place safe); o[0] is never stored.
+__device__ __forceinline__ constexpr int mirror_x(int s) { return s == 2 ? 4 : s == 4 ? 2 : s == 5 ? 8 : s == 8 ? 5 : s == 6 ? 7 : s == 7 ? 6 : s; }
+__device__ __forceinline__ constexpr int mirror_y(int s) { return s == 1 ? 3 : s == 3 ? 1 : s == 5 ? 6 : s == 6 ? 5 : s == 7 ? 8 : s == 8 ? 7 : s; }
+template <typename T, bool NORMAL_X> __device__ __forceinline__ void reflect(const T (&f)[9], T (&o)[9])
+{
+#pragma unroll
+	for (int s = 0; s < 9; s++) o[s] = f[NORMAL_X ? mirror_x(s) : mirror_y(s)];
+}
+
+// columns the two out-of-vector neighbours are pulled from: wrapped (LB.c:337-338) or, with open ends ("fluid flows
+// out of the domain", LB.c:42: the reference names the option, its WRAPAROUND macro is dead), the end column itself --
+// a zero-gradient end: what would be pulled from beyond the lattice is the same speed of the end column's own site in
+// that row, and what streams past the end is dropped.
+template <typename T> __device__ __forceinline__ void pull_columns(const StepParams<T> &p, int j0, int V, int &jl, int &jr)
+{
+	jl = j0 == 0 ? (p.outflow ? 0 : p.ny - 1) : j0 - 1;
+	jr = j0 + V == p.ny ? (p.outflow ? p.ny - 1 : 0) : j0 + V;
+}
+
 // ApplySource (LB.c:489-518) on the nine values of one fluid site of column 0
 template <typename T> __device__ __forceinline__ void source_site(T (&o)[9], const StepParams<T> &p)
 {
@@ -284,13 +310,21 @@ __device__ __forceinline__ uint32_t relax_sites(const StepParams<T> &p, const T 
 	const uint32_t bits = (word >> sh) & ((1u << V) - 1u);
 	bool dbl = false;
 	if (sizeof(T) == 4) dbl = ((word >> (sh & ~(uint32_t)(p.vw - 1))) & ((1u << p.vw) - 1u)) != 0u;
+	uint32_t sx = 0u, sy = 0u;                               // slip walls among my V sites (subsets of `bits`)
+	if (bits != 0u && p.slip != nullptr) {
+		const size_t w = (size_t)r * p.ldw + (j0 >> 5);
+		sx = (__ldg(p.slip + w) >> sh) & bits;
+		sy = (__ldg(p.slip + (size_t)p.nxl * p.ldw + w) >> sh) & bits;
+	}
 #pragma unroll
 	for (int k = 0; k < V; k++) {
 		T fk[9], ok[9];
 #pragma unroll
 		for (int s = 0; s < 9; s++) fk[s] = f[s][k];
 		if ((bits >> k) & 1u) {
-			bounce<T>(fk, ok);
+			if ((sx >> k) & 1u) reflect<T, true>(fk, ok);
+			else if ((sy >> k) & 1u) reflect<T, false>(fk, ok);
+			else bounce<T>(fk, ok);
 		} else {
 			collide_vec_order<T>(fk, ok, p, dbl);
 			if (k == 0 && j0 == 0 && tail_source) source_site<T>(ok, p);
@@ -305,36 +339,24 @@ __device__ __forceinline__ uint32_t relax_sites(const StepParams<T> &p, const T 
 // the fused pull update of one V-wide vector of sites (StreamCollideVec, LB.c:307-484,
 // + tail ApplySource + halo push)
 //   V     sites per thread (contiguous in j, V*sizeof(T) <= 32 bytes)
-//   NB    0: +-1 column element from the adjacent lane (shuffle), 1: direct load
-//   HINT  0: default caching, 1: L1::no_allocate loads + .cs stores, 2: L2-coherent (.cg) loads
-//   WRAP  true: rows wrap inside this slab (no halo rows read or written) -- the persistent
-//         multi-step kernel; false: rows i-1/i+1 come from the halo rows, boundary rows push
-// All 32 lanes of a warp must call this together (shuffles); `active` predicates the stores.
+//   HINT  0: default caching, 1: L1::no_allocate loads + .cs stores
+// Rows i-1 / i+1 come from the halo rows (the periodic wrap of a single slab, the seam of a ring); threads of the
+// first / last owned row push the three speeds the neighbour will pull into its halo row.
 // ---------------------------------------------------------------------------
-template <typename T, int V, int NB, int HINT, bool WRAP>
-__device__ __forceinline__ void update_vector(const StepParams<T> &p, const T *__restrict__ src, T *__restrict__ dst,
-                                              uint32_t nvec, uint32_t g, bool active, uint32_t lane, int tail_source)
+template <typename T, int V, int HINT>
+__device__ __forceinline__ void update_vector(const StepParams<T> &p, uint32_t nvec, uint32_t g)
 {
 	const uint32_t rr = g / nvec;
 	const uint32_t jv = g - rr * nvec;
 	const int r = p.r0 + (int)rr;                            // owned row; storage row r+1
 	const int j0 = p.jmin + (int)jv * V;
-
-	// wrapped columns of the two out-of-vector neighbours (LB.c:337-338)
-	const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
-	const int jr = j0 + V == p.ny ? 0 : j0 + V;
-	const bool edge_l = (NB == 1) || V == 1 || lane == 0 || jv == 0;
-	const bool edge_r = (NB == 1) || V == 1 || lane == 31 || jv == nvec - 1;
+	int jl, jr;
+	pull_columns(p, j0, V, jl, jr);
 
 	const T *row[3];                                         // rows i-1, i, i+1 of the source
-	row[1] = src + (size_t)(r + 1) * p.ldy;
-	if (WRAP) {                                              // x_d, x_u of LB.c:335-336
-		row[0] = src + (size_t)(r == 0 ? p.nxl : r) * p.ldy;
-		row[2] = src + (size_t)(r == p.nxl - 1 ? 1 : r + 2) * p.ldy;
-	} else {                                                 // halo rows make the wrap / the slab seam
-		row[0] = row[1] - p.ldy;
-		row[2] = row[1] + p.ldy;
-	}
+	row[1] = p.src + (size_t)(r + 1) * p.ldy;
+	row[0] = row[1] - p.ldy;
+	row[2] = row[1] + p.ldy;
 
 	T f[9][V];
 #pragma unroll
@@ -350,17 +372,11 @@ __device__ __forceinline__ void update_vector(const StepParams<T> &p, const T *_
 #pragma unroll
 				for (int k = 0; k < V; k++) f[s][k] = own[k];
 			} else if (pull_dj(s) < 0) {                     // element k comes from column j0+k-1
-				T nb = T(0);
-				if (NB == 0) nb = __shfl_up_sync(0xffffffffu, own[V - 1], 1);
-				if (edge_l) nb = ld1<HINT>(base_s + jl);
-				f[s][0] = nb;
+				f[s][0] = ld1<HINT>(base_s + jl);
 #pragma unroll
 				for (int k = 1; k < V; k++) f[s][k] = own[k - 1];
 			} else {                                         // element k comes from column j0+k+1
-				T nb = T(0);
-				if (NB == 0) nb = __shfl_down_sync(0xffffffffu, own[0], 1);
-				if (edge_r) nb = ld1<HINT>(base_s + jr);
-				f[s][V - 1] = nb;
+				f[s][V - 1] = ld1<HINT>(base_s + jr);
 #pragma unroll
 				for (int k = 0; k < V - 1; k++) f[s][k] = own[k + 1];
 			}
@@ -368,34 +384,30 @@ __device__ __forceinline__ void update_vector(const StepParams<T> &p, const T *_
 	}
 
 	T o[9][V];
-	const uint32_t bits = relax_sites<T, V>(p, f, o, r, j0, tail_source);
+	const uint32_t bits = relax_sites<T, V>(p, f, o, r, j0, p.tail_source);
 
-	if (active) {
-		T *d = dst + (size_t)(r + 1) * p.ldy + j0;
-		if (bits == 0u) stv<HINT, V>(d, o[0]);
-		else {
+	T *d = p.dst + (size_t)(r + 1) * p.ldy + j0;
+	if (bits == 0u) stv<HINT, V>(d, o[0]);
+	else {
 #pragma unroll
-			for (int k = 0; k < V; k++) if (!((bits >> k) & 1u)) d[k] = o[0][k];     // f0 untouched at walls
-		}
+		for (int k = 0; k < V; k++) if (!((bits >> k) & 1u)) d[k] = o[0][k];     // f0 untouched at walls
+	}
 #pragma unroll
-		for (int s = 1; s < 9; s++) stv<HINT, V>(d + (size_t)s * p.plane, o[s]);
-		if (!WRAP) {
-			if (r == 0) {                                    // what the slab below pulls from its row "hi" (LB.c:239,242,243)
-				stv<HINT, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
-				stv<HINT, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
-				stv<HINT, V>(p.dn_halo + 8 * p.dn_plane + j0, o[8]);
-			}
-			if (r == p.nxl - 1) {                            // what the slab above pulls from its row "lo-1" (LB.c:237,240,241)
-				stv<HINT, V>(p.up_halo + 2 * p.up_plane + j0, o[2]);
-				stv<HINT, V>(p.up_halo + 5 * p.up_plane + j0, o[5]);
-				stv<HINT, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
-			}
-		}
+	for (int s = 1; s < 9; s++) stv<HINT, V>(d + (size_t)s * p.plane, o[s]);
+	if (r == 0) {                                            // what the slab below pulls from its row "hi" (LB.c:239,242,243)
+		stv<HINT, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
+		stv<HINT, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
+		stv<HINT, V>(p.dn_halo + 8 * p.dn_plane + j0, o[8]);
+	}
+	if (r == p.nxl - 1) {                                    // what the slab above pulls from its row "lo-1" (LB.c:237,240,241)
+		stv<HINT, V>(p.up_halo + 2 * p.up_plane + j0, o[2]);
+		stv<HINT, V>(p.up_halo + 5 * p.up_plane + j0, o[5]);
+		stv<HINT, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
 	}
 }
 
-// One lattice step per launch.  1-D grid, blockDim multiple of 32; grid-stride over (row, vector) pairs.
-template <typename T, int V, int NB, int HINT>
+// One lattice step per launch.  1-D grid; grid-stride over (row, vector) pairs.
+template <typename T, int V, int HINT>
 __global__ void __launch_bounds__(512)
 stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 {
@@ -404,15 +416,10 @@ stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
 	const uint32_t total = (uint32_t)(p.r1 - p.r0) * nvec;
-	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t stride = gridDim.x * blockDim.x;
 	asm volatile("griddepcontrol.wait;" ::: "memory");
-	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {   // warp-uniform trip count
-		const uint32_t g0 = base + threadIdx.x;
-		const bool active = g0 < total;
-		const uint32_t g = active ? g0 : total - 1;          // idle lanes shadow the last vector (loads stay legal)
-		update_vector<T, V, NB, HINT, false>(p, p.src, p.dst, nvec, g, active, lane, p.tail_source);
-	}
+	for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += stride)
+		update_vector<T, V, HINT>(p, nvec, g);
 }
 
 // ---------------------------------------------------------------------------
@@ -436,34 +443,33 @@ stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 // memory, or this slab itself when P == 1); phase 2 pushes the three halo speeds like the A/B
 // kernel does.  Same bytes over NVLink per two steps as A/B.
 // ---------------------------------------------------------------------------
-// CG: ld.global.cg (L2 only) -- for the dataflow kernel, whose CTAs read what other SMs wrote during the same launch
-template <bool CG, typename X> __device__ __forceinline__ X ld_coh(const X *p)
+// coherent loads (never ld.global.nc: the buffer is written by the same kernel)
+template <int V> __device__ __forceinline__ void ldc(const double *p, double (&v)[V])
 {
-	if constexpr (CG) return __ldcg(p);
-	else return *p;
-}
-template <int V, bool CG = false> __device__ __forceinline__ void ldc(const double *p, double (&v)[V])
-{
-	if constexpr (V == 1) v[0] = ld_coh<CG>(p);
+	if constexpr (V == 1) v[0] = *p;
 	else {
 #pragma unroll
-		for (int k = 0; k < V; k += 2) { const double2 t = ld_coh<CG>(reinterpret_cast<const double2 *>(p + k)); v[k] = t.x; v[k + 1] = t.y; }
+		for (int k = 0; k < V; k += 2) { const double2 t = *reinterpret_cast<const double2 *>(p + k); v[k] = t.x; v[k + 1] = t.y; }
 	}
 }
-template <int V, bool CG = false> __device__ __forceinline__ void ldc(const float *p, float (&v)[V])
+template <int V> __device__ __forceinline__ void ldc(const float *p, float (&v)[V])
 {
-	if constexpr (V == 1) v[0] = ld_coh<CG>(p);
-	else if constexpr (V == 2) { const float2 t = ld_coh<CG>(reinterpret_cast<const float2 *>(p)); v[0] = t.x; v[1] = t.y; }
+	if constexpr (V == 1) v[0] = *p;
+	else if constexpr (V == 2) { const float2 t = *reinterpret_cast<const float2 *>(p); v[0] = t.x; v[1] = t.y; }
 	else {
 #pragma unroll
-		for (int k = 0; k < V; k += 4) { const float4 t = ld_coh<CG>(reinterpret_cast<const float4 *>(p + k)); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
+		for (int k = 0; k < V; k += 4) { const float4 t = *reinterpret_cast<const float4 *>(p + k); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
 	}
 }
-// V values to columns (j0-1 .. j0+V-2) [DJ < 0, first one wraps to jl] or (j0+1 .. j0+V) [DJ > 0, last one wraps to jr]
-template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(T *row, int j0, int jl, int jr, const T (&v)[V])
+// V values to columns (j0-1 .. j0+V-2) [DJ < 0, the first one goes to jl] or (j0+1 .. j0+V) [DJ > 0, the last one goes to jr].
+// Periodic ends: jl / jr are the wrapped columns.  Open ends (outflow): what would leave the lattice is dropped and the
+// end column's site stores a second copy of the value that stays at the end (the zero-gradient end of pull_columns()):
+// the slot the wrap would have filled.
+template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(T *row, int j0, int jl, int jr, int ny, int outflow, const T (&v)[V])
 {
 	if constexpr (DJ < 0) {
-		row[jl] = v[0];
+		if (!(outflow && j0 == 0)) row[jl] = v[0];
+		if (outflow && j0 + V == ny) row[ny - 1] = v[V - 1];
 		if constexpr (V == 2) row[j0] = v[1];
 		if constexpr (V >= 4) {
 #pragma unroll
@@ -474,7 +480,8 @@ template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(
 			row[j0 + V - 2] = v[V - 1];
 		}
 	} else {
-		row[jr] = v[V - 1];
+		if (!(outflow && j0 + V == ny)) row[jr] = v[V - 1];
+		if (outflow && j0 == 0) row[0] = v[0];
 		if constexpr (V == 2) row[j0 + 1] = v[0];
 		if constexpr (V >= 4) {
 			row[j0 + 1] = v[0];
@@ -488,49 +495,55 @@ template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(
 }
 
 // the nine populations the V sites (r, j0..j0+V-1) relax this step
-template <typename T, int V, int PHASE, bool CG = false>
+template <typename T, int V, int PHASE>
 __device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T (&f)[9][V])
 {
 	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;    // p.src == p.dst
 	if constexpr (PHASE == 2) {
 #pragma unroll
-		for (int s = 0; s < 9; s++) ldc<V, CG>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
+		for (int s = 0; s < 9; s++) ldc<V>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
 	} else {
-		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;          // LB.c:337-338
-		const int jr = j0 + V == p.ny ? 0 : j0 + V;
+		int jl, jr;
+		pull_columns(p, j0, V, jl, jr);
 		const T *lrow[3] = {own - p.ldy, own, own + p.ldy};  // rows i-1 (halo when r == 0), i, i+1 (halo when r == nxl-1)
 #pragma unroll
 		for (int s = 0; s < 9; s++) {
 			const T *b = lrow[pull_di(s) + 1] + (size_t)s * p.plane;
 			if constexpr (V == 1) {
-				f[s][0] = ld_coh<CG>(b + (pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0));
+				f[s][0] = b[pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0];
 			} else {
 				T al[V];
-				ldc<V, CG>(b + j0, al);
+				ldc<V>(b + j0, al);
 				if (pull_dj(s) == 0) {
 #pragma unroll
 					for (int k = 0; k < V; k++) f[s][k] = al[k];
 				} else if (pull_dj(s) < 0) {
-					f[s][0] = ld_coh<CG>(b + jl);
+					f[s][0] = b[jl];
 #pragma unroll
 					for (int k = 1; k < V; k++) f[s][k] = al[k - 1];
 				} else {
-					f[s][V - 1] = ld_coh<CG>(b + jr);
+					f[s][V - 1] = b[jr];
 #pragma unroll
 					for (int k = 0; k < V - 1; k++) f[s][k] = al[k + 1];
 				}
 			}
 		}
+		// Open ends only: the end column's site reads a slot its in-row neighbour also reads and then overwrites (the one
+		// slot with two readers).  Both are lanes of one warp (V == 1: adjacent lanes, column ranges start at multiples
+		// of 8; V > 1: one thread); order every lane's loads before any lane's stores.
+		if (p.outflow) __syncwarp();
 	}
 }
 
-template <typename T, int V, int PHASE>
+// HINT 1: streaming (evict-first) stores -- the last level of a temporal-blocking macro-step, whose results are not read
+// again before the tile has left L2 anyway
+template <typename T, int V, int PHASE, int HINT>
 __device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, const T (&o)[9][V])
 {
 	T *const own = p.dst + (size_t)(r + 1) * p.ldy;
 	if constexpr (PHASE == 2) {
 #pragma unroll
-		for (int s = 0; s < 9; s++) stv<0, V>(own + (size_t)s * p.plane + j0, o[s]);
+		for (int s = 0; s < 9; s++) stv<HINT, V>(own + (size_t)s * p.plane + j0, o[s]);
 		if (r == 0) {                                        // as in the A/B kernel (LB.c:239,242,243)
 			stv<0, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
 			stv<0, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
@@ -542,8 +555,8 @@ __device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, 
 			stv<0, V>(p.up_halo + 6 * p.up_plane + j0, o[6]);
 		}
 	} else {
-		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
-		const int jr = j0 + V == p.ny ? 0 : j0 + V;
+		int jl, jr;
+		pull_columns(p, j0, V, jl, jr);
 		// slot k of site (x - e_k) receives o[opp(k)]; rows beyond the slab are the neighbour's owned boundary rows
 		T *srow[3];
 		size_t spl[3];
@@ -553,99 +566,9 @@ __device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, 
 #pragma unroll
 		for (int k = 0; k < 9; k++) {
 			T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
-			if (pull_dj(k) == 0) stv<0, V>(b + j0, o[opposite(k)]);
-			else if (pull_dj(k) < 0) st_shifted<T, V, -1>(b, j0, jl, jr, o[opposite(k)]);
-			else st_shifted<T, V, 1>(b, j0, jl, jr, o[opposite(k)]);
-		}
-	}
-}
-
-// ---------------------------------------------------------------------------
-// Phase 1 with every global access an ALIGNED vector (V > 1): the element a shifted stream needs from column
-// j0-1 / j0+V is the adjacent lane's aligned load (warp shuffle), and the element a thread owes to the
-// adjacent lane's aligned vector travels the same way before the store; only the lanes at a warp edge or at
-// an end of the row's column range fall back to one scalar access.  Safe in place: the shuffled element
-// belongs to the receiving thread's own site set, and a warp issues its loads before its stores.
-// All 32 lanes must call these (idle lanes shadow the last vector of the range and do not store).
-// ---------------------------------------------------------------------------
-template <typename T, int V>
-__device__ __forceinline__ void aa_load_shf(const StepParams<T> &p, int r, int j0, bool edge_l, bool edge_r, T (&f)[9][V])
-{
-	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;
-	const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
-	const int jr = j0 + V == p.ny ? 0 : j0 + V;
-	const T *lrow[3] = {own - p.ldy, own, own + p.ldy};
-#pragma unroll
-	for (int s = 0; s < 9; s++) {
-		const T *b = lrow[pull_di(s) + 1] + (size_t)s * p.plane;
-		T al[V];
-		ldc<V>(b + j0, al);
-		if (pull_dj(s) == 0) {
-#pragma unroll
-			for (int k = 0; k < V; k++) f[s][k] = al[k];
-		} else if (pull_dj(s) < 0) {
-			T nb = __shfl_up_sync(0xffffffffu, al[V - 1], 1);
-			if (edge_l) nb = b[jl];
-			f[s][0] = nb;
-#pragma unroll
-			for (int k = 1; k < V; k++) f[s][k] = al[k - 1];
-		} else {
-			T nb = __shfl_down_sync(0xffffffffu, al[0], 1);
-			if (edge_r) nb = b[jr];
-			f[s][V - 1] = nb;
-#pragma unroll
-			for (int k = 0; k < V - 1; k++) f[s][k] = al[k + 1];
-		}
-	}
-}
-
-template <typename T, int V>
-__device__ __forceinline__ void aa_store_shf(const StepParams<T> &p, int r, int j0, bool edge_l, bool edge_r, bool active, const T (&o)[9][V])
-{
-	T *const own = p.dst + (size_t)(r + 1) * p.ldy;
-	const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
-	const int jr = j0 + V == p.ny ? 0 : j0 + V;
-	T *srow[3];
-	size_t spl[3];
-	srow[1] = own;              spl[1] = p.plane;
-	if (r == 0) { srow[0] = p.dn_halo - p.ldy; spl[0] = p.dn_plane; } else { srow[0] = own - p.ldy; spl[0] = p.plane; }
-	if (r == p.nxl - 1) { srow[2] = p.up_halo + p.ldy; spl[2] = p.up_plane; } else { srow[2] = own + p.ldy; spl[2] = p.plane; }
-#pragma unroll
-	for (int k = 0; k < 9; k++) {
-		T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
-		const T (&v)[V] = o[opposite(k)];
-		if (pull_dj(k) == 0) {
-			if (active) stv<0, V>(b + j0, v);
-		} else if (pull_dj(k) < 0) {                         // my values belong at columns j0-1 .. j0+V-2
-			const T recv = __shfl_down_sync(0xffffffffu, v[0], 1);   // the right lane's first value: my vector's last column
-			if (active) {
-				if (!edge_r) {
-					T w[V];
-#pragma unroll
-					for (int m = 0; m < V - 1; m++) w[m] = v[m + 1];
-					w[V - 1] = recv;
-					stv<0, V>(b + j0, w);
-				} else {
-#pragma unroll
-					for (int m = 1; m < V; m++) b[j0 + m - 1] = v[m];
-				}
-				if (edge_l) b[jl] = v[0];
-			}
-		} else {                                             // my values belong at columns j0+1 .. j0+V
-			const T recv = __shfl_up_sync(0xffffffffu, v[V - 1], 1);  // the left lane's last value: my vector's first column
-			if (active) {
-				if (!edge_l) {
-					T w[V];
-					w[0] = recv;
-#pragma unroll
-					for (int m = 1; m < V; m++) w[m] = v[m - 1];
-					stv<0, V>(b + j0, w);
-				} else {
-#pragma unroll
-					for (int m = 0; m < V - 1; m++) b[j0 + m + 1] = v[m];
-				}
-				if (edge_r) b[jr] = v[V - 1];
-			}
+			if (pull_dj(k) == 0) stv<HINT, V>(b + j0, o[opposite(k)]);
+			else if (pull_dj(k) < 0) st_shifted<T, V, -1>(b, j0, jl, jr, p.ny, p.outflow, o[opposite(k)]);
+			else st_shifted<T, V, 1>(b, j0, jl, jr, p.ny, p.outflow, o[opposite(k)]);
 		}
 	}
 }
@@ -657,22 +580,17 @@ template <typename T> __device__ __forceinline__ int aa_row(const StepParams<T> 
 	return r >= p.nxl ? r - p.nxl : r;
 }
 
-// 2-D grid: x over the vectors of a row, y over rows -- no integer division per site.
-// PIPE == 0: one row per thread and pass (grid-stride over y).
-// PIPE == 1: each thread walks rows blockIdx.y, +gridDim.y, ... and loads the populations of its NEXT
-//            row before it relaxes the current one (two register sets, ping-pong), so the L2 latency
-//            of the loads is covered by ~300 instructions of arithmetic.  For the L2-resident runs
-//            (in-place small lattices, temporal blocking) that are bound by load latency at the
-//            occupancy 60-120 registers allow.  Safe in place: a site's nine slots are its own.
-#ifdef LBM_AA_MINB      /* experiment builds (tools/): 128-thread CTAs, at least LBM_AA_MINB of them per SM */
-#define LBM_AA_BOUNDS __launch_bounds__(128, LBM_AA_MINB)
-#else
+// One in-place step over rows [r0, r1) x columns [jmin, jmax) (either range may wrap).  2-D grid: x over the vectors
+// of a row, y over rows (grid-stride above 65535 rows) -- no integer division per site.
 // SP: CTAs of at most 256 threads, four of them per SM -> 64 registers.  Measured on the L2-resident 400x4000 lattice
 // (profiles/r01_run24/occ_probe_sp.log): phase 1 at vec 4 drops from 104 registers / 22.4 us to 64 / 17.7 us, the
 // run from 113.2 to 119.7 GLUPS.  DP (54-58 registers at vec 1) gains nothing from a cap (profiles/r01_run12).
+#ifdef LBM_AA_MINB      /* experiment builds (tools/): 128-thread CTAs, at least LBM_AA_MINB of them per SM */
+#define LBM_AA_BOUNDS __launch_bounds__(128, LBM_AA_MINB)
+#else
 #define LBM_AA_BOUNDS __launch_bounds__(sizeof(T) == 4 ? 256 : 512, sizeof(T) == 4 ? 4 : 0)
 #endif
-template <typename T, int V, int PHASE, int PIPE>
+template <typename T, int V, int PHASE, int HINT>
 __global__ void LBM_AA_BOUNDS
 stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 {
@@ -683,573 +601,14 @@ stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 	int j0 = p.jmin + (int)jv * V;
 	if (j0 >= p.ny) j0 -= p.ny;                              // column ranges of the 2-D wavefront schedule may wrap (jmax > ny)
 	asm volatile("griddepcontrol.wait;" ::: "memory");
-	if constexpr (PIPE == 2 && PHASE == 1 && V > 1) {            // PIPE == 2: the aligned-access (warp shuffle) phase 1
-		const bool active = jv < nvec;
-		const uint32_t jc = active ? jv : nvec - 1;              // idle lanes shadow the last vector (loads stay legal)
-		int jj = p.jmin + (int)jc * V;
-		if (jj >= p.ny) jj -= p.ny;
-		const uint32_t lane = threadIdx.x & 31u;
-		const bool edge_l = lane == 0 || jc == 0, edge_r = lane == 31 || jc >= nvec - 1;
-		for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
-			const int r = aa_row(p, rr);
-			T f[9][V], o[9][V];
-			aa_load_shf<T, V>(p, r, jj, edge_l, edge_r, f);
-			relax_sites<T, V>(p, f, o, r, jj, p.tail_source);
-			aa_store_shf<T, V>(p, r, jj, edge_l, edge_r, active, o);
-		}
-		return;
-	}
-	if (jv >= nvec) return;
-	if constexpr (PIPE != 1) {
-		for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
-			const int r = aa_row(p, rr);
-			T f[9][V], o[9][V];
-			aa_load<T, V, PHASE>(p, r, j0, f);
-			relax_sites<T, V>(p, f, o, r, j0, p.tail_source);
-			aa_store<T, V, PHASE>(p, r, j0, o);
-		}
-	} else {
-		uint32_t rr = blockIdx.y;
-		if (rr >= rows) return;
-		const uint32_t st = gridDim.y;
-		T fa[9][V], fb[9][V], o[9][V];
-		aa_load<T, V, PHASE>(p, aa_row(p, rr), j0, fa);
-#pragma unroll 1
-		for (; rr < rows; rr += st) {
-			const int r = aa_row(p, rr);
-			const uint32_t nx = rr + st < rows ? rr + st : rr;       // last row: a harmless reload of its own (already consumed) slots
-			aa_load<T, V, PHASE>(p, aa_row(p, nx), j0, fb);
-			relax_sites<T, V>(p, fa, o, r, j0, p.tail_source);
-			aa_store<T, V, PHASE>(p, r, j0, o);
-#pragma unroll
-			for (int s = 0; s < 9; s++)
-#pragma unroll
-				for (int k = 0; k < V; k++) fa[s][k] = fb[s][k];
-		}
-	}
-}
-
-// ---------------------------------------------------------------------------
-// In-place step, one site per thread, threads walking rows blockIdx.y, +gridDim.y, ... like PIPE == 1 -- but the nine
-// populations of the NEXT row travel global -> shared memory with cp.async (LDGSTS, 4 or 8 bytes per copy, each thread
-// its own nine) while the current row is relaxed, instead of into a second register set: the L2 latency is covered
-// without the registers that cost PIPE == 1 its occupancy, and without the serial load -> arithmetic -> store of a
-// looping thread (capped grids, DESIGN.md "What did NOT help" (2), (8)).  No barrier: a thread reads only what it copied
-// itself (cp.async.wait_group).  Safe in place for the reason PIPE == 1 is: a site's nine slots are its own.
-// Dynamic shared memory: 2 x 9 x blockDim.x elements.
-// STATUS: written after the round-1 GPU budget was spent; compiles (SASS: LDGSTS), not yet run on a GPU.  Off unless
-// lbm_tuning.stage_smem is set; its GPU test is gated by LBM_TEST_EXPERIMENTAL=1.
-// ---------------------------------------------------------------------------
-template <typename T> __device__ __forceinline__ void cp_async_elem(T *smem_dst, const T *gsrc)
-{
-	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-	asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gsrc), "n"(sizeof(T)) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// same addresses as aa_load<T, 1, PHASE>; dst = this thread's element of stage slot s, slots `stride` elements apart
-template <typename T, int PHASE>
-__device__ __forceinline__ void aa_stage_issue(const StepParams<T> &p, int r, int j0, T *dst, uint32_t stride)
-{
-	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;
-	if constexpr (PHASE == 2) {
-#pragma unroll
-		for (int s = 0; s < 9; s++) cp_async_elem<T>(dst + s * stride, own + (size_t)opposite(s) * p.plane + j0);
-	} else {
-		const int jl = j0 == 0 ? p.ny - 1 : j0 - 1;
-		const int jr = j0 + 1 == p.ny ? 0 : j0 + 1;
-		const T *lrow[3] = {own - p.ldy, own, own + p.ldy};
-#pragma unroll
-		for (int s = 0; s < 9; s++)
-			cp_async_elem<T>(dst + s * stride, lrow[pull_di(s) + 1] + (size_t)s * p.plane + (pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0));
-	}
-}
-
-template <typename T, int PHASE>
-__global__ void __launch_bounds__(256)
-stream_collide_aa_staged_kernel(const __grid_constant__ StepParams<T> p)
-{
-	extern __shared__ __align__(16) unsigned char aa_stage_raw[];
-	T *const stage = reinterpret_cast<T *>(aa_stage_raw);        // [2][9][blockDim.x]
-	asm volatile("griddepcontrol.launch_dependents;");
-	const uint32_t ncol = (uint32_t)(p.jmax - p.jmin);
-	const uint32_t rows = (uint32_t)(p.r1 - p.r0);
-	const uint32_t jv = blockIdx.x * blockDim.x + threadIdx.x;
-	int j0 = p.jmin + (int)jv;
-	if (j0 >= p.ny) j0 -= p.ny;
-	asm volatile("griddepcontrol.wait;" ::: "memory");
-	uint32_t rr = blockIdx.y;
-	if (jv >= ncol || rr >= rows) return;
-	const uint32_t st = gridDim.y, bd = blockDim.x;
-	T *const mine = stage + threadIdx.x;
-	aa_stage_issue<T, PHASE>(p, aa_row(p, rr), j0, mine, bd);
-	cp_async_commit();
-	uint32_t b = 0;
-#pragma unroll 1
-	for (; rr < rows; rr += st) {
+	if (jv >= nvec) return;                                  // (exited lanes do not take part in aa_load's __syncwarp())
+	for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
 		const int r = aa_row(p, rr);
-		if (rr + st < rows) aa_stage_issue<T, PHASE>(p, aa_row(p, rr + st), j0, mine + (b ^ 1u) * 9u * bd, bd);
-		cp_async_commit();                                       // (possibly empty) so that "all but the newest group" is this row's
-		cp_async_wait<1>();
-		T f[9][1], o[9][1];
-#pragma unroll
-		for (int s = 0; s < 9; s++) f[s][0] = mine[(b * 9u + (uint32_t)s) * bd];
-		relax_sites<T, 1>(p, f, o, r, j0, p.tail_source);
-		aa_store<T, 1, PHASE>(p, r, j0, o);
-		b ^= 1u;
+		T f[9][V], o[9][V];
+		aa_load<T, V, PHASE>(p, r, j0, f);
+		relax_sites<T, V>(p, f, o, r, j0, p.tail_source);
+		aa_store<T, V, PHASE, HINT>(p, r, j0, o);
 	}
-}
-
-// ---------------------------------------------------------------------------
-// Phase 2 with TMA (1-D bulk copies): the phase is local and aligned, so what a CTA needs for a row segment of
-// blockDim.x sites is nine contiguous pieces of memory in and nine out.  Thread 0 moves them with cp.async.bulk
-// (global -> shared completing on an mbarrier; shared -> global as a bulk group), two stages each way; every thread
-// is left with 9 LDS, relax_sites and 9 STS at 32-bit shared addresses -- no global address arithmetic, no load
-// latency in any thread.  CTAs walk rows blockIdx.y, +gridDim.y, ...; whole rows only (segments must not wrap).
-//   iteration i:  T0: loads of row i+1 -> in[b^1] (read last in iteration i-1, before its barrier)
-//                 all: wait full[b]; LDS; relax; STS -> out[b]; fence.proxy.async
-//                 T0: wait until the bulk stores of iterations <= i-1 have read their shared source (that of i-1
-//                     reads out[b^1], which iteration i+1 overwrites after this iteration's barrier)
-//                 barrier;  T0: bulk store out[b] -> global
-// Dynamic shared memory: (2 x 9 + 2 x 9) x blockDim.x elements + two mbarriers.
-// STATUS: like stream_collide_aa_staged_kernel -- compiled (SASS: UBLKCP, SYNCS), not yet run on a GPU;
-// lbm_tuning.stage_smem = 2 selects it for phase 2 (phase 1 then runs the cp.async kernel above).
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
-{
-	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
-{
-	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
-{
-	uint32_t ok;
-	do {
-		asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-		             : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-	} while (!ok);
-}
-__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar)
-{
-	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-	             ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void *gdst, const void *smem_src, uint32_t bytes)
-{
-	asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
-}
-
-template <typename T>
-__global__ void __launch_bounds__(128)
-stream_collide_aa_bulk2_kernel(const __grid_constant__ StepParams<T> p)
-{
-	extern __shared__ __align__(128) unsigned char aa_bulk_raw[];
-	const uint32_t B = blockDim.x;
-	T *const in = reinterpret_cast<T *>(aa_bulk_raw);            // [2][9][B]
-	T *const out = in + 2u * 9u * B;                             // [2][9][B]
-	uint64_t *const full = reinterpret_cast<uint64_t *>(out + 2u * 9u * B);   // [2]
-	asm volatile("griddepcontrol.launch_dependents;");
-	const int c0 = (int)(blockIdx.x * B);
-	const uint32_t ncols = (uint32_t)min((int)B, p.ny - c0);
-	const uint32_t bytes = ncols * (uint32_t)sizeof(T);          // multiple of 16: ny is a multiple of the vector width
-	const bool live = threadIdx.x < ncols;
-	const int j0 = c0 + (int)threadIdx.x;
-	const uint32_t rows = (uint32_t)(p.r1 - p.r0), st = gridDim.y;
-	if (threadIdx.x == 0) {
-		mbar_init(&full[0], 1);
-		mbar_init(&full[1], 1);
-		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-	}
-	__syncthreads();
-	asm volatile("griddepcontrol.wait;" ::: "memory");
-	uint32_t rr = blockIdx.y;
-	if (rr >= rows) return;
-	auto issue_loads = [&](int r, uint32_t stage) {              // thread 0 only
-		const T *const own = p.dst + (size_t)(r + 1) * p.ldy + c0;
-		mbar_expect_tx(&full[stage], 9u * bytes);
-#pragma unroll
-		for (int s = 0; s < 9; s++) bulk_g2s(in + (stage * 9u + (uint32_t)s) * B, own + (size_t)opposite(s) * p.plane, bytes, &full[stage]);
-	};
-	if (threadIdx.x == 0) issue_loads(aa_row(p, rr), 0);
-	uint32_t b = 0, parity = 0;                                  // bit b of `parity`: phase of full[b] to wait for
-#pragma unroll 1
-	for (; rr < rows; rr += st) {
-		const int r = aa_row(p, rr);
-		if (threadIdx.x == 0 && rr + st < rows) issue_loads(aa_row(p, rr + st), b ^ 1u);
-		mbar_wait(&full[b], (parity >> b) & 1u);
-		parity ^= 1u << b;
-		if (live) {
-			T f[9][1], o[9][1];
-#pragma unroll
-			for (int s = 0; s < 9; s++) f[s][0] = in[(b * 9u + (uint32_t)s) * B + threadIdx.x];
-			relax_sites<T, 1>(p, f, o, r, j0, p.tail_source);
-#pragma unroll
-			for (int s = 0; s < 9; s++) out[(b * 9u + (uint32_t)s) * B + threadIdx.x] = o[s][0];
-			if (r == 0) {                                        // halo pushes as in aa_store<T, 1, 2>
-				p.dn_halo[4 * p.dn_plane + j0] = o[4][0]; p.dn_halo[7 * p.dn_plane + j0] = o[7][0]; p.dn_halo[8 * p.dn_plane + j0] = o[8][0];
-			}
-			if (r == p.nxl - 1) {
-				p.up_halo[2 * p.up_plane + j0] = o[2][0]; p.up_halo[5 * p.up_plane + j0] = o[5][0]; p.up_halo[6 * p.up_plane + j0] = o[6][0];
-			}
-		}
-		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // my STS before the bulk store reads them
-		if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-		__syncthreads();
-		if (threadIdx.x == 0) {
-			T *const own = p.dst + (size_t)(r + 1) * p.ldy + c0;
-#pragma unroll
-			for (int s = 0; s < 9; s++) bulk_s2g(own + (size_t)s * p.plane, out + (b * 9u + (uint32_t)s) * B, bytes);
-			asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-		}
-		b ^= 1u;
-	}
-	if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-// ---------------------------------------------------------------------------
-// Persistent multi-step kernel for lattices whose step is short (tens of microseconds): ONE
-// cooperative launch runs `nsteps` lattice steps.  Each CTA owns a fixed contiguous range of the
-// flattened (row, vector) space; instead of a grid-wide barrier per step, a CTA starts step t as
-// soon as the CTAs owning the rows above/below its range have finished step t-1 (their progress
-// counters, polled with acquire loads) -- the D2Q9 pull only reaches one row and one column away
-// (LB.c:235-243), and the same condition covers the write-after-read hazard of the A/B buffers.
-// No launch gaps, no per-step ramp-up/drain.  Source data is read with .cg (L2-coherent) loads:
-// L1 is not coherent across CTAs and the same addresses are rewritten every second step.
-// ---------------------------------------------------------------------------
-struct PersistParams {
-	int nsteps;
-	int last_tail_source;       // tail_source of the last step (0: leave A un-sourced, LB.c:192-205)
-	uint32_t chunk;             // vectors per CTA (multiple of 32)
-	int *progress;              // [gridDim.x] completed steps per CTA, zeroed before launch
-	int *abort;                 // set when a wait timed out
-	unsigned long long timeout_ns;
-};
-
-__device__ __forceinline__ int ld_acquire_gpu(const int *p)
-{
-	int v;
-	asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-	return v;
-}
-__device__ __forceinline__ void st_release_gpu(int *p, int v)
-{
-	asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-template <typename T, int V, int NB>
-__global__ void __launch_bounds__(512)
-stream_collide_persistent_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ PersistParams q)
-{
-	const uint32_t nvec = (uint32_t)(p.jmax - p.jmin) / V;
-	const uint32_t total = (uint32_t)p.nxl * nvec;           // r0 == 0, r1 == nxl
-	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t lo = blockIdx.x * q.chunk;
-	const uint32_t hi = min(lo + q.chunk, total);
-	__shared__ int s_abort, s_ndeps;
-	__shared__ uint32_t s_dep0[3], s_depn[3];
-
-	// CTAs whose ranges touch [lo - 2*nvec, hi + 2*nvec] (periodic in the flattened index): one row up
-	// and down, plus the y-wrap of the diagonal pulls at j = 0 and j = ny-1 (e.g. f8 of (r, 0) comes
-	// from (r+1, ny-1) = g + 2*nvec - 1).  Up to three runs of consecutive CTA ids.
-	if (threadIdx.x == 0) {
-		s_abort = 0;
-		const long long a0 = (long long)lo - 2ll * nvec, b0 = (long long)hi + 2ll * nvec;
-		int n = 0;
-		if ((unsigned long long)(b0 - a0 + 1) >= total) {    // tiny lattice: depend on everybody
-			s_dep0[0] = 0; s_depn[0] = gridDim.x; n = 1;
-		} else {
-			const uint32_t ia = (uint32_t)max(a0, 0ll) / q.chunk, ib = (uint32_t)min(b0, (long long)total - 1) / q.chunk;
-			s_dep0[n] = ia; s_depn[n] = ib - ia + 1; n++;
-			if (a0 < 0) { const uint32_t ja = (uint32_t)(a0 + total) / q.chunk, jb = (total - 1) / q.chunk; s_dep0[n] = ja; s_depn[n] = jb - ja + 1; n++; }
-			if (b0 >= (long long)total) { const uint32_t jb = (uint32_t)(b0 - total) / q.chunk; s_dep0[n] = 0; s_depn[n] = jb + 1; n++; }
-		}
-		s_ndeps = n;
-	}
-	__syncthreads();
-
-	const T *src = p.src;
-	T *dst = p.dst;
-	for (int t = 0; t < q.nsteps; t++) {
-		if (t > 0) {
-			if (threadIdx.x < 32) {                          // warp 0: one dependency per lane, polled concurrently
-				unsigned long long t0 = 0;
-				uint32_t spins = 0;
-				for (int k = 0; k < s_ndeps; k++)
-					for (uint32_t c = s_dep0[k] + lane; c < s_dep0[k] + s_depn[k]; c += 32)
-						while (ld_acquire_gpu(q.progress + c) < t) {
-							if ((++spins & 255u) != 0) continue;         // look at the clock only now and then
-							unsigned long long now;
-							asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-							if (t0 == 0) t0 = now;
-							if (now - t0 > q.timeout_ns || ld_acquire_gpu(q.abort)) { *q.abort = 1; s_abort = 1; break; }
-						}
-			}
-			__syncthreads();
-			if (s_abort) return;
-		}
-		const int tail = (t == q.nsteps - 1) ? q.last_tail_source : 1;
-		for (uint32_t base = lo; base < hi; base += blockDim.x) {                    // warp-uniform trip count
-			const uint32_t g0 = base + threadIdx.x;
-			const bool active = g0 < hi;
-			const uint32_t g = active ? g0 : hi - 1;
-			update_vector<T, V, NB, 2, true>(p, src, dst, nvec, g, active, lane, tail);
-		}
-		__syncthreads();                                     // all of this CTA's stores issued ...
-		if (threadIdx.x == 0) {
-			__threadfence();                                 // ... and visible device-wide before the counter moves
-			st_release_gpu(q.progress + blockIdx.x, t + 1);
-		}
-		const T *tmp = src; src = dst; dst = const_cast<T *>(tmp);
-	}
-}
-
-// ---------------------------------------------------------------------------
-// Dataflow form of the temporally blocked in-place engine (single slab, full-width row bands): ONE launch runs a
-// whole macro-step, i.e. every (row piece, level) of the wavefront schedule.  The list of those "launches" is cut
-// into items of one row x one column chunk; CTA b takes items b, b + gridDim.x, ... in list order.  What the
-// kernel boundary between two levels used to guarantee is checked per item instead: (level s, row r) starts when
-// rows r-1, r, r+1 (periodic) have finished level s-1 -- the only dependency the in-place kernels have (read
-// after write; see the temporal blocking notes in lbm_api.cu) -- read from per-(level,row) counters of finished
-// chunks.  The list order is a topological order (tests/test_tb_schedule.py) and all CTAs are co-resident
-// (cooperative launch), so the lowest unfinished item can always run: no deadlock.  No drain / refill between
-// the ~60 short launches of a macro-step; the small inverted-pyramid levels hide between the big ones.
-// Level 0 depends on the previous macro-step only, i.e. on the previous launch.
-// ---------------------------------------------------------------------------
-struct DfLaunch {
-	int level, r0, rows, tail_source;
-	unsigned first;             // index of this launch's first item
-};
-struct DfParams {
-	const DfLaunch *list;
-	int nlaunch;
-	unsigned nitems;
-	int chunks;                 // column chunks per row
-	int iters;                  // vectors per thread and item; a chunk is blockDim.x * iters vectors
-	int *cnt;                   // [levels][nxl] finished chunks, zeroed before the launch
-	int *abort;                 // set when a wait timed out
-	int levels;
-	unsigned long long timeout_ns;
-};
-
-// Both phases in one kernel: left alone ptxas spends 88 registers on the vec-1 DP instance (the phase kernels take 56-59,
-// and the L2-resident DP kernel loses 15 % at 104, profiles/r01_run25/NOTE.md) -- capped at 64 like the SP kernels.
-#ifndef LBM_DF_MINB
-#define LBM_DF_MINB 8
-#endif
-struct DfItem { int level, r, tail_source; unsigned ch; };
-
-__device__ __forceinline__ DfItem df_locate(const DfParams &q, unsigned n, int &cur, int nxl)
-{
-	while (cur + 1 < q.nlaunch && n >= q.list[cur + 1].first) cur++;
-	const DfLaunch L = q.list[cur];
-	const unsigned local = n - L.first;
-	const unsigned rr = local / (unsigned)q.chunks;
-	DfItem it;
-	it.level = L.level; it.tail_source = L.tail_source;
-	it.ch = local - rr * (unsigned)q.chunks;
-	it.r = L.r0 + (int)rr;
-	if (it.r >= nxl) it.r -= nxl;
-	return it;
-}
-// the counter thread `t` (0..2) of a CTA watches for an item: row r-1+t of the level below
-__device__ __forceinline__ const int *df_dep(const DfParams &q, const DfItem &it, int t, int nxl)
-{
-	int rd = it.r - 1 + t;
-	if (rd < 0) rd += nxl;
-	if (rd >= nxl) rd -= nxl;
-	return q.cnt + (size_t)(it.level - 1) * nxl + rd;
-}
-__device__ __forceinline__ void red_release_gpu_add(int *p, int v)
-{
-	asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-template <typename T, int V, bool CG>
-__global__ void __launch_bounds__(sizeof(T) == 4 ? 256 : 128, sizeof(T) == 4 ? 4 : LBM_DF_MINB)
-stream_collide_aa_dataflow_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ DfParams q)
-{
-	const uint32_t nvec = (uint32_t)p.ny / V;
-	__shared__ int s_abort;
-	if (threadIdx.x == 0) s_abort = 0;
-	const bool watcher = threadIdx.x < 3;
-	int cur = 0;
-	unsigned n = blockIdx.x;
-	if (n >= q.nitems) return;
-	DfItem it = df_locate(q, n, cur, p.nxl);
-	int seen = (watcher && it.level > 0) ? ld_acquire_gpu(df_dep(q, it, (int)threadIdx.x, p.nxl)) : q.chunks;
-	for (;;) {
-		if (watcher && it.level > 0 && seen < q.chunks) {        // usually already seen full one item ago (below)
-			const int *c = df_dep(q, it, (int)threadIdx.x, p.nxl);
-			unsigned long long t0 = 0;
-			uint32_t spins = 0;
-			while (ld_acquire_gpu(c) < q.chunks) {
-				if ((++spins & 255u) != 0) continue;
-				unsigned long long now;
-				asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-				if (t0 == 0) t0 = now;
-				if (now - t0 > q.timeout_ns || ld_acquire_gpu(q.abort)) { *q.abort = 1; s_abort = 1; break; }
-			}
-		}
-		__syncthreads();
-		if (s_abort) return;
-		// next item of this CTA: look at its counters now, the answer arrives while this item is computed
-		const unsigned nn = n + gridDim.x;
-		DfItem nit = it;
-		if (nn < q.nitems) {
-			nit = df_locate(q, nn, cur, p.nxl);
-			seen = (watcher && nit.level > 0) ? ld_acquire_gpu(df_dep(q, nit, (int)threadIdx.x, p.nxl)) : q.chunks;
-		}
-		const uint32_t v0 = it.ch * blockDim.x * (uint32_t)q.iters + threadIdx.x;
-		for (int u = 0; u < q.iters; u++) {
-			const uint32_t jv = v0 + (uint32_t)u * blockDim.x;
-			if (jv < nvec) {
-				const int j0 = (int)jv * V;
-				T f[9][V], o[9][V];
-				if (it.level & 1) {
-					aa_load<T, V, 2, CG>(p, it.r, j0, f);
-					relax_sites<T, V>(p, f, o, it.r, j0, it.tail_source);
-					aa_store<T, V, 2>(p, it.r, j0, o);
-				} else {
-					aa_load<T, V, 1, CG>(p, it.r, j0, f);
-					relax_sites<T, V>(p, f, o, it.r, j0, it.tail_source);
-					aa_store<T, V, 1>(p, it.r, j0, o);
-				}
-			}
-		}
-		__syncthreads();                                         // all of this item's stores issued ...
-		if (threadIdx.x == 0)                                    // ... and visible device-wide before the row's counter moves
-			red_release_gpu_add(q.cnt + (size_t)it.level * p.nxl + it.r, 1);
-		if (nn >= q.nitems) return;
-		n = nn; it = nit;
-	}
-}
-
-// ---------------------------------------------------------------------------
-// Fused pair: phase 2 of one step and phase 1 of the next in ONE pass over memory.
-//   Phase 2 is local (site x relaxes the nine slots of x), phase 1 of the following step pulls f_s from slot s of
-//   x + pull(s) -- i.e. the phase-2 result o_s of that neighbour.  A CTA owns a tile of `tile_rows` rows x TC
-//   columns, one thread per column, and walks the rows: at row r it runs phase 2 of (r, c), leaves the nine
-//   results in a ring of rows in shared memory, and then runs phase 1 of (r-1, c) from the ring.  For a site
-//   whose 3x3 neighbourhood lies inside the tile ("interior") the intermediate populations never travel: 9 loads
-//   and 9 stores for TWO timesteps, half the traffic of the two separate kernels (to L2 and, where the lattice
-//   does not fit it, to HBM).
-//   Sites on the rim of a tile ("edge": first/last row, first/last column) cannot take phase 1 here (a neighbour's
-//   phase-2 result belongs to another CTA); they store their phase-2 result the ordinary way and
-//   stream_collide_aa_edges_kernel gives them phase 1 afterwards.  That kernel reads slot k of interior sites next to
-//   the rim as well, so an interior site stores o_k into its slot k wherever the slot's consumer x - pull(k) is an
-//   edge site; every other slot of an interior site receives the phase-1 result of its interior consumer, exactly
-//   where the ordinary phase 1 puts it.  Each slot is written by one thread per sub-step and tiles read and write
-//   their own sites only: no ordering between CTAs is needed.  Same relax_sites() as everywhere: bit-identical.
-//   Rows 0 and nxl-1 of a slab must be tile edges (their halo traffic is the ordinary kernels' business).
-// ---------------------------------------------------------------------------
-struct PairParams {
-	int tile_rows;              // rows per tile (>= 3 for any interior)
-	int tail_source2;           // tail_source of the phase-1 half (StepParams.tail_source is the phase-2 half's)
-};
-
-#ifndef LBM_PAIR_MINB
-#define LBM_PAIR_MINB 0
-#endif
-template <typename T, int TC>
-__global__ void __launch_bounds__(TC, LBM_PAIR_MINB)
-stream_collide_aa_pair_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ PairParams q)
-{
-	asm volatile("griddepcontrol.launch_dependents;");
-	// four-row ring: row r is written while rows r-3..r-1 may still be read, so one barrier per row is enough (a thread
-	// reaches the write of row r+2, which reuses the slot of r-2, only past the barrier of row r+1, i.e. after every
-	// thread has finished reading for row r)
-	__shared__ T sh[4][9][TC];
-	const int j = (int)threadIdx.x;
-	const int c0 = (int)blockIdx.x * TC;
-	const int c1 = min(c0 + TC, p.ny);
-	const int c = c0 + j;
-	const bool live = c < c1;
-	const bool col_edge = c == c0 || c == c1 - 1;
-	const int tr0 = p.r0 + (int)blockIdx.y * q.tile_rows;
-	const int tr1 = min(tr0 + q.tile_rows, p.r1);
-	asm volatile("griddepcontrol.wait;" ::: "memory");
-	// the nine populations of row r are loaded one row ahead (nothing writes a row of this tile before its own phase 2
-	// has read it: phase 1 of row r-1 reaches rows r-2..r only, and other CTAs never write this tile's sites)
-	T fn[9][1];
-	if (live) aa_load<T, 1, 2>(p, tr0, c, fn);
-	int cur = 0;                                             // ring slot of row r; row r-1 in (cur+3)&3, row r-2 in (cur+2)&3
-	for (int r = tr0; r < tr1; r++) {
-		if (live) {
-			T f[9][1], o[9][1];
-#pragma unroll
-			for (int s = 0; s < 9; s++) f[s][0] = fn[s][0];
-			if (r + 1 < tr1) aa_load<T, 1, 2>(p, r + 1, c, fn);
-			relax_sites<T, 1>(p, f, o, r, c, p.tail_source);
-#pragma unroll
-			for (int s = 0; s < 9; s++) sh[cur][s][j] = o[s][0];
-			if (col_edge || r == tr0 || r == tr1 - 1) {
-				aa_store<T, 1, 2>(p, r, c, o);
-			} else {
-				T *const own = p.dst + (size_t)(r + 1) * p.ldy + c;
-				const bool dn = r - 1 == tr0, up = r + 1 == tr1 - 1, lf = c - 1 == c0, rt = c + 1 == c1 - 1;
-#pragma unroll
-				for (int k = 1; k < 9; k++) {                    // consumer of slot k: site (r - pull_di(k), c - pull_dj(k))
-					const bool row_hit = pull_di(k) > 0 ? dn : pull_di(k) < 0 ? up : false;
-					const bool col_hit = pull_dj(k) > 0 ? lf : pull_dj(k) < 0 ? rt : false;
-					if (row_hit || col_hit) own[(size_t)k * p.plane] = o[k][0];
-				}
-			}
-		}
-		__syncthreads();
-		if (live && !col_edge && r - 1 > tr0) {                  // phase 1 of (r-1, c): rows r-2, r-1, r are in the ring
-			const int slot_of[3] = {(cur + 2) & 3, (cur + 3) & 3, cur};
-			T f[9][1], o[9][1];
-#pragma unroll
-			for (int s = 0; s < 9; s++) f[s][0] = sh[slot_of[pull_di(s) + 1]][s][j + pull_dj(s)];
-			relax_sites<T, 1>(p, f, o, r - 1, c, q.tail_source2);
-			aa_store<T, 1, 1>(p, r - 1, c, o);
-		}
-		cur = (cur + 1) & 3;
-	}
-}
-
-// phase 1 for the sites the pair kernel left out: the first and last row of every row tile (whole rows), and the first
-// and last column of every column tile in the other rows.  blockIdx.y < edge_rows: row ordinal; beyond: rows of the
-// launch's range, threads over the column-tile rims.
-struct EdgeParams {
-	int tile_rows, tile_cols;
-	int edge_rows;              // 2 per row tile
-	int col_tiles;
-};
-
-template <typename T>
-__global__ void __launch_bounds__(128)
-stream_collide_aa_edges_kernel(const __grid_constant__ StepParams<T> p, const __grid_constant__ EdgeParams q)
-{
-	asm volatile("griddepcontrol.launch_dependents;");
-	int r, c;
-	if ((int)blockIdx.y < q.edge_rows) {
-		const int t = (int)blockIdx.y >> 1;
-		const int tr0 = p.r0 + t * q.tile_rows, tr1 = min(tr0 + q.tile_rows, p.r1);
-		r = (blockIdx.y & 1) ? tr1 - 1 : tr0;
-		if ((blockIdx.y & 1) && tr1 - 1 == tr0) return;          // one-row tile: once
-		c = (int)(blockIdx.x * blockDim.x + threadIdx.x);
-		if (c >= p.ny) return;
-	} else {
-		r = p.r0 + (int)blockIdx.y - q.edge_rows;
-		const int rel = (r - p.r0) % q.tile_rows;
-		if (rel == 0 || rel == q.tile_rows - 1 || r == p.r1 - 1) return;     // a tile's first / last row: done above
-		const int e = (int)(blockIdx.x * blockDim.x + threadIdx.x);
-		if (e >= 2 * q.col_tiles) return;
-		const int c0 = (e >> 1) * q.tile_cols, c1 = min(c0 + q.tile_cols, p.ny);
-		c = (e & 1) ? c1 - 1 : c0;
-		if ((e & 1) && c1 - 1 == c0) return;
-	}
-	asm volatile("griddepcontrol.wait;" ::: "memory");
-	T f[9][1], o[9][1];
-	aa_load<T, 1, 1>(p, r, c, f);
-	relax_sites<T, 1>(p, f, o, r, c, p.tail_source);
-	aa_store<T, 1, 1>(p, r, c, o);
 }
 
 // ---------------------------------------------------------------------------
@@ -1269,8 +628,8 @@ stream_collide_scalar_kernel(const __grid_constant__ StepParams<T> p)
 		int r = p.r0 + (int)rr;
 		if (PHASE != 0 && r >= p.nxl) r -= p.nxl;            // in-place wavefront schedule: wrapping row range
 		const int j = p.jmin + (int)(g - rr * ncol);
-		const int jl = j == 0 ? p.ny - 1 : j - 1;
-		const int jr = j + 1 == p.ny ? 0 : j + 1;
+		int jl, jr;                                          // open ends (p.outflow): the A/B phase only, lbm_create refuses the rest
+		pull_columns(p, j, 1, jl, jr);
 		T f[9], o[9];
 		if (PHASE == 0) {
 			const T *row0 = p.src + (size_t)r * p.ldy;
@@ -1292,8 +651,16 @@ stream_collide_scalar_kernel(const __grid_constant__ StepParams<T> p)
 			for (int s = 0; s < 9; s++) f[s] = site[(size_t)opposite(s) * p.plane];
 		}
 		const bool wall = (__ldg(p.mask + (size_t)r * p.ldw + (j >> 5)) >> (j & 31)) & 1u;
-		if (wall) bounce<T>(f, o);
-		else {
+		if (wall) {
+			uint32_t kind = 0u;
+			if (p.slip != nullptr) {
+				const size_t w = (size_t)r * p.ldw + (j >> 5);
+				kind = ((__ldg(p.slip + w) >> (j & 31)) & 1u) | (((__ldg(p.slip + (size_t)p.nxl * p.ldw + w) >> (j & 31)) & 1u) << 1);
+			}
+			if (kind & 1u) reflect<T, true>(f, o);
+			else if (kind & 2u) reflect<T, false>(f, o);
+			else bounce<T>(f, o);
+		} else {
 			collide_scalar_order<T>(f, o, p);
 			if (j == 0 && p.tail_source) source_site<T>(o, p);
 		}
@@ -1383,7 +750,7 @@ __global__ void halo_unpack_kernel(T *f, const T *from_dn, const T *from_up, siz
 
 // Scene description, evaluated per site (InitializeArrays, LB.c:559-578, plus a disc)
 struct SceneDev {
-	int nx, channel_walls;
+	int nx, channel_walls;                 // channel_walls 2: rows 0 and nx-1 are "reflect" (slip) walls, normal x
 	int bar_i0, bar_i1, bar_j0, bar_j1;
 	long long disc_ci, disc_cj, disc_r2;   // disc_r2 < 0: none
 };
@@ -1397,18 +764,29 @@ __device__ __forceinline__ bool scene_is_wall(const SceneDev &sc, int gi, int j)
 	}
 	return false;
 }
-// one thread per mask word
-__global__ void scene_mask_kernel(uint32_t *mask, SceneDev sc, int row_lo, int nxl, int ny, int ldw)
+// one thread per mask word; slip = [2][nxl][ldw] bit planes of the reflect walls (only the channel rows can be one)
+__global__ void scene_mask_kernel(uint32_t *mask, uint32_t *slip, SceneDev sc, int row_lo, int nxl, int ny, int ldw)
 {
 	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= (size_t)nxl * ldw) return;
 	const int r = (int)(g / ldw), w = (int)(g % ldw);
-	uint32_t bits = 0;
+	const int gi = row_lo + r;
+	uint32_t bits = 0, sx = 0;
 	for (int b = 0; b < 32; b++) {
 		const int j = w * 32 + b;
-		if (j < ny && scene_is_wall(sc, row_lo + r, j)) bits |= 1u << b;
+		if (j < ny && scene_is_wall(sc, gi, j)) bits |= 1u << b;
+	}
+	if (sc.channel_walls == 2 && (gi == 0 || gi == sc.nx - 1)) {
+		SceneDev inner = sc;                                     // sites of the channel rows that are NOT also barrier / disc sites
+		inner.channel_walls = 0;
+		for (int b = 0; b < 32; b++) {
+			const int j = w * 32 + b;
+			if (j < ny && !scene_is_wall(inner, gi, j)) sx |= 1u << b;
+		}
 	}
 	mask[g] = bits;
+	slip[g] = sx;
+	slip[(size_t)nxl * ldw + g] = 0u;
 }
 // 32-bit integer hash (lowbias32) -- the closed-form density perturbation of lbm_scene.perturb_seed
 __host__ __device__ __forceinline__ uint32_t hash32(uint32_t x)
@@ -1498,28 +876,40 @@ nonfinite_kernel(const T *f, size_t plane, int ldy, int nxl, int ny, unsigned lo
 	if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out, (unsigned long long)bad);
 }
 
-// walls chars [nxl][ldc] -> bit words; *bad is set if a value other than 0/1 is seen
-__global__ void mask_pack_kernel(const char *walls, size_t ldc, uint32_t *mask, int nxl, int ny, int ldw, int *bad)
+// walls chars [nxl][ldc] -> bit planes: mask = any wall (1, 2, 3); slip[0] = value 2 (reflect, normal x), slip[1] = value 3
+// (reflect, normal y).  flags[0] is set if another value is seen, flags[1] if any reflect wall is.
+__global__ void mask_pack_kernel(const char *walls, size_t ldc, uint32_t *mask, uint32_t *slip, int nxl, int ny, int ldw, int *flags)
 {
 	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= (size_t)nxl * ldw) return;
 	const int r = (int)(g / ldw), w = (int)(g % ldw);
-	uint32_t bits = 0;
+	uint32_t bits = 0, sx = 0, sy = 0;
 	for (int b = 0; b < 32; b++) {
 		const int j = w * 32 + b;
 		if (j < ny) {
 			const char c = walls[(size_t)r * ldc + j];
-			if (c == 1) bits |= 1u << b; else if (c != 0) *bad = 1;
+			if (c == 1 || c == 2 || c == 3) bits |= 1u << b; else if (c != 0) flags[0] = 1;
+			if (c == 2) sx |= 1u << b;
+			if (c == 3) sy |= 1u << b;
 		}
 	}
 	mask[g] = bits;
+	slip[g] = sx;
+	slip[(size_t)nxl * ldw + g] = sy;
+	if (sx | sy) flags[1] = 1;
 }
-__global__ void mask_unpack_kernel(const uint32_t *mask, char *walls, size_t ldc, int nxl, int ny, int ldw)
+__global__ void mask_unpack_kernel(const uint32_t *mask, const uint32_t *slip, char *walls, size_t ldc, int nxl, int ny, int ldw)
 {
 	const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= (size_t)nxl * ny) return;
 	const int r = (int)(g / ny), j = (int)(g % ny);
-	walls[(size_t)r * ldc + j] = (char)((mask[(size_t)r * ldw + (j >> 5)] >> (j & 31)) & 1u);
+	const size_t w = (size_t)r * ldw + (j >> 5);
+	char v = (char)((mask[w] >> (j & 31)) & 1u);
+	if (v && slip) {
+		if ((slip[w] >> (j & 31)) & 1u) v = 2;
+		else if ((slip[(size_t)nxl * ldw + w] >> (j & 31)) & 1u) v = 3;
+	}
+	walls[(size_t)r * ldc + j] = v;
 }
 
 // rho, u_x, u_y in the order of PrintLattice / ComputeReynolds (LB.c:621-629, 535-540).

@@ -17,14 +17,16 @@ def _ptr(a):
 
 
 class Lattice:
-    def __init__(self, nx, ny, prec="dp", tau=0.7, accel=0.005, vecwidth=0, device=0, row_lo=0, row_hi=0, inplace=False):
+    def __init__(self, nx, ny, prec="dp", tau=0.7, accel=0.005, vecwidth=0, device=0, row_lo=0, row_hi=0, inplace=False,
+                 outflow=False, experimental=False):
         """``inplace=True`` keeps ONE buffer and steps with the in-place (AA) kernels: buffer A after every
-        even step count is bit-identical, buffer B does not exist (lbm_config.inplace)."""
-        self.lib = _capi.load(prec)
+        even step count is bit-identical, buffer B does not exist (lbm_config.inplace).  ``outflow=True``: open y ends
+        (lbm_config.boundary_y = LBM_Y_OUTFLOW).  ``experimental=True`` loads the experiment build (exp/)."""
+        self.lib = _capi.load(prec, experimental)
         self.inplace = bool(inplace)
         self.prec, self.dtype = prec, self.lib.dtype
         self.nx, self.ny = int(nx), int(ny)
-        cfg = self.lib.Config(self.nx, self.ny, tau, accel, vecwidth, device, row_lo, row_hi, int(self.inplace))
+        cfg = self.lib.Config(self.nx, self.ny, tau, accel, vecwidth, device, row_lo, row_hi, int(self.inplace), int(bool(outflow)))
         self._ctx = ctypes.c_void_p()
         self.lib.check(self.lib.dll.lbm_create(ctypes.byref(self._ctx), ctypes.byref(cfg)))
         self.tau = cfg.tau
@@ -72,6 +74,17 @@ class Lattice:
         fB = None if fB is None else np.ascontiguousarray(fB, dtype=self.dtype)
         assert fA.size == 9 * self.nx * ldy and walls.size == self.nx * ldy
         self._call("lbm_upload", _ptr(fA), _ptr(fB), _ptr(walls), ldy)
+
+    def set_walls(self, walls, ldy=None):
+        """The wall mask alone (global layout): 0 fluid, 1 bounce-back, 2 / 3 reflect with normal x / y (lbm_set_walls)."""
+        ldy = self.ny if ldy is None else ldy
+        walls = np.ascontiguousarray(walls, dtype=np.int8)
+        assert walls.size == self.nx * ldy
+        self._call("lbm_set_walls", _ptr(walls), ldy)
+
+    def load_walls(self, path):
+        """Geometry from a text file (lbm_load_walls): one lattice row per line, entries 0..3."""
+        self._call("lbm_load_walls", str(path).encode())
 
     def download(self, which="A", out=None, ldy=None):
         """Returns (9,nx,ldy); rows outside this slab are left as they were in ``out`` (zeros if new)."""
@@ -196,6 +209,11 @@ class Lattice:
             setattr(t, k, v)
         self._call("lbm_set_tuning", ctypes.byref(t))
 
+    def set_experimental(self, **kw):
+        """Experiment build only (include/lbm_b200_experimental.h): stage_smem, rows_per_thread."""
+        x = self.lib.Experimental(**kw)
+        self._call("lbm_set_experimental", ctypes.byref(x))
+
     def get_tuning(self):
         t = self.lib.Tuning()
         self._call("lbm_get_tuning", ctypes.byref(t))
@@ -213,6 +231,13 @@ def group_run(slabs, nsteps):
     lib.check(lib.dll.lbm_group_run(arr, len(slabs), int(nsteps)))
 
 
+def print_lattice_group(slabs, path):
+    """PrintLattice (LB.c:610-639) of a lattice spread over in-process slabs: one CSV, rows in order."""
+    lib = slabs[0].lib
+    arr = (ctypes.c_void_p * len(slabs))(*[s._ctx.value for s in slabs])
+    lib.check(lib.dll.lbm_print_lattice_group(arr, len(slabs), str(path).encode()))
+
+
 def make_ring(nx, ny, nslabs, prec="dp", device=0, bounds=None, **kw):
     """Split rows [0,nx) into ``nslabs`` contiguous slabs on one device and wire them as a ring --
     decomposition-invariance tests without a cluster."""
@@ -226,15 +251,14 @@ def make_ring(nx, ny, nslabs, prec="dp", device=0, bounds=None, **kw):
     return slabs
 
 
-def tb_schedule(nx, ny, tb_depth, tb_rows=0, tb_cols=0, prec="dp", multi=False, dataflow=False):
+def tb_schedule(nx, ny, tb_depth, tb_rows=0, tb_cols=0, prec="dp", multi=False):
     """Launch list of one temporal-blocking macro-step (lbm_tb_schedule; host logic, no GPU):
     returns (depth_used, [(level, r0, r1, j0, j1), ...]); ranges past nx / ny wrap periodically,
     j0 == j1 == 0 means whole rows.  ``multi=True``: the list of one slab of a multi-slab ring, each entry
-    with a sixth field ``seam`` (bit 0: wait for the neighbours' previous event first, bit 1: announce after).
-    ``dataflow=True``: the order in which the dataflow kernel (``Tuning.dataflow``) takes a single slab's launches."""
+    with a sixth field ``seam`` (bit 0: wait for the neighbours' previous event first, bit 1: announce after)."""
     lib = _capi.load(prec)
     k = ctypes.c_int()
-    mode = 2 if dataflow else int(bool(multi))
+    mode = int(bool(multi))
     n = lib.dll.lbm_tb_schedule(nx, ny, mode, tb_depth, tb_rows, tb_cols, ctypes.byref(k), None, 0)
     if n < 0:
         raise _capi.LbmError(_capi.ERR_ARG, lib.dll.lbm_last_error().decode())

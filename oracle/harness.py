@@ -168,3 +168,7 @@ class Ref(_Base):
 
     def reynolds(self):
         return float(self.lib.ComputeReynolds(self._p(self.fA), self._p(self.walls)))
+
+    def print_lattice(self, time_step):
+        """The reference's own PrintLattice (LB.c:610-639): writes data/<time_step>.csv under the CURRENT directory."""
+        self.lib.PrintLattice(int(time_step), self._p(self.fA))

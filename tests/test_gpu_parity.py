@@ -46,23 +46,16 @@ def _assert_same(got, want, what):
 # ---------------------------------------------------------------------------------------------
 # against the golden vectors of the compiled reference (every case, incl. 10,000 steps)
 # ---------------------------------------------------------------------------------------------
-ENGINES = {"default": {}, "persistent": dict(persistent=1), "pdl": dict(pdl=1), "graph": dict(graph=3),
-           "graph+pdl": dict(graph=4, pdl=1),
+ENGINES = {"default": {}, "pdl": dict(pdl=1), "graph": dict(graph=3), "graph+pdl": dict(graph=4, pdl=1), "hints": dict(hints=1, vec=2),
            # one buffer, in-place (AA) kernels (lbm_config.inplace): only buffer A exists
            "inplace": dict(inplace=1), "inplace+graph+pdl": dict(inplace=1, graph=4, pdl=1),
            # + temporal blocking in L2: bands of tb_rows rows advanced tb_depth steps each (wavefront schedule)
            "inplace+tb": dict(inplace=1, tb_depth=4, tb_rows=3),
            "inplace+tb+graph+pdl": dict(inplace=1, tb_depth=6, tb_rows=5, graph=1, pdl=1),
-           "inplace+tb+pipe": dict(inplace=1, tb_depth=8, tb_rows=12, rows_per_thread=3, vec=1, graph=1, pdl=1),
-           # 2-D tiles: column strips as well as row bands (falls back to bands where ny is not a multiple of 8)
+           # 2-D tiles: column strips as well as row bands (falls back to bands where ny is not a multiple of 8);
+           # hints: the last level of every macro-step stores with the evict-first policy
            "inplace+tb2d": dict(inplace=1, tb_depth=4, tb_rows=16, tb_cols=256, graph=1, pdl=1),
-           # phase 1 with aligned vector accesses only, +-1 column elements exchanged by warp shuffles
-           "inplace+shuffle": dict(inplace=1, neighbour=0), "inplace+shuffle+tb2d": dict(inplace=1, neighbour=0, vec=2, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1),
-           # a whole macro-step of the wavefront schedule in ONE launch, per-row dependency counters instead of kernel boundaries
-           "inplace+dataflow": dict(inplace=1, tb_depth=8, tb_rows=12, tb_cols=1 << 20, vec=1, dataflow=1),
-           "inplace+dataflow+l1": dict(inplace=1, tb_depth=6, tb_cols=1 << 20, dataflow=3, hints=1, block=64),
-           # phase 2 of a step and phase 1 of the next fused in one kernel (tiles of fuse_rows x block sites, shared memory)
-           "inplace+pairs": dict(inplace=1, fuse_rows=5, pdl=1), "inplace+pairs64": dict(inplace=1, fuse_rows=9, block=64, tb_depth=0)}
+           "inplace+tb2d+hints": dict(inplace=1, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1, hints=1, vec=2)}
 
 
 def _split(engine_kw):
@@ -76,7 +69,7 @@ def _split(engine_kw):
 @pytest.mark.parametrize("name", list(cases.CASES))
 def test_cuda_matches_reference_golden(name, engine):
     c, g = cases.CASES[name], GOLDEN[name]
-    if engine in ("pdl", "graph", "inplace+tb2d", "inplace+shuffle+tb2d") and c["steps"] > 1000:
+    if engine in ("pdl", "graph", "hints", "inplace+tb2d", "inplace+tb2d+hints") and c["steps"] > 1000:
         pytest.skip("10,000-step cases: not under the plain pdl/graph engines, nor under the deliberately tiny 2-D tiles "
                     "(tens of millions of launches); the in-place defaults cover temporal blocking at full length")
     fA, walls = cases.make_inputs(name)
@@ -133,18 +126,11 @@ def _variants(prec):
     vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
     out = []
     for v in vecs:
-        for nb in (0, 1):
-            for hints in (0, 1):
-                out.append(dict(vec=v, neighbour=nb, hints=hints, block=256, ctas_per_sm=0, persistent=0))
-            out.append(dict(vec=v, neighbour=nb, hints=0, block=128, ctas_per_sm=0, persistent=1))
-    out += [dict(vec=vecs[-1], neighbour=0, hints=0, block=128, ctas_per_sm=2, persistent=0),
-            dict(vec=2, neighbour=0, hints=1, block=512, ctas_per_sm=1, persistent=0),
-            dict(vec=2, neighbour=0, hints=0, block=64, ctas_per_sm=8, persistent=0),
-            dict(vec=2, neighbour=0, hints=0, block=512, ctas_per_sm=1, persistent=1),
-            dict(vec=vecs[-1], neighbour=1, hints=0, block=64, ctas_per_sm=3, persistent=1),
-            dict(vec=1, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=1, graph=2),
-            dict(vec=vecs[-1], neighbour=0, hints=1, block=256, ctas_per_sm=4, persistent=0, pdl=1, graph=0),
-            dict(vec=2, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=0, graph=1)]
+        for hints in (0, 1):
+            out.append(dict(vec=v, hints=hints, block=256))
+    out += [dict(vec=vecs[-1], hints=0, block=128), dict(vec=2, hints=1, block=512), dict(vec=2, hints=0, block=64),
+            dict(vec=1, hints=0, block=128, pdl=1, graph=2), dict(vec=vecs[-1], hints=1, block=256, pdl=1, graph=0),
+            dict(vec=2, hints=0, block=128, pdl=0, graph=1)]
     return out
 
 
@@ -160,33 +146,23 @@ def test_every_kernel_variant_is_bit_identical(prec):
             lat.run(c["steps"])
             _assert_same(lat.download("A"), o.f_view("A"), f"fA with {tune}")
             _assert_same(lat.download("B"), o.f_view("B"), f"fB with {tune}")
-    # the in-place kernels: every vector width, a few CTA shapes, capped grids, PDL/graph
+    # the in-place kernels: every vector width, a few CTA shapes, PDL/graph
     vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
     with _lattice(c, inplace=True) as lat:
         for v in vecs:
-            for extra in (dict(block=128), dict(block=256, ctas_per_sm=2), dict(block=64, pdl=1, graph=2), dict(block=512, ctas_per_sm=1, pdl=1),
-                          dict(block=128, neighbour=0), dict(block=96, neighbour=0, ctas_per_sm=1), dict(block=32, neighbour=0, tb_depth=4, tb_rows=11, tb_cols=40),
-                          dict(block=128, vec_phase1=2 if v != 2 else 1), dict(block=64, vec_phase1=vecs[-1], neighbour=0, pdl=1, graph=1)):
-                tune = dict(dict(vec=v, neighbour=1, hints=0, ctas_per_sm=0, persistent=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0, vec_phase1=0), **extra)
+            for extra in (dict(block=128), dict(block=256), dict(block=64, pdl=1, graph=2), dict(block=512, pdl=1), dict(block=96),
+                          dict(block=32, tb_depth=4, tb_rows=11, tb_cols=40), dict(block=128, hints=1, tb_depth=2, tb_rows=30)):
+                tune = dict(dict(vec=v, hints=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0), **extra)
                 lat.set_tuning(**tune)
                 lat.upload(fA, walls)
                 lat.run(4)
                 lat.run(c["steps"] - 4)
                 _assert_same(lat.download("A"), o.f_view("A"), f"in-place fA with {tune}")
-        # software-pipelined in-place kernels (each thread walks rows_per_thread rows, loads one row ahead)
-        for v, rpt, extra in ((1, 2, {}), (1, 5, dict(tb_depth=4, tb_rows=9)), (2, 3, dict(pdl=1, graph=2)), (2, 96, {}),
-                              (1, 7, dict(ctas_per_sm=1, block=64)), (vecs[-1], 4, {})):
-            tune = dict(dict(vec=v, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=0, graph=0, tb_depth=0, tb_rows=0,
-                             rows_per_thread=rpt), **extra)
-            lat.set_tuning(**tune)
-            lat.upload(fA, walls)
-            lat.run(c["steps"])
-            _assert_same(lat.download("A"), o.f_view("A"), f"pipelined in-place fA with {tune}")
-        lat.set_tuning(rows_per_thread=0)
-        # wavefront schedules: depth k, band height H (0 = automatic), with and without graph replay
+        # wavefront schedules: depth k, band height H (0 = automatic), with and without graph replay, with and without
+        # evict-first stores on the last level
         for k, h, g, w in ((2, 0, 0, 0), (4, 7, 0, 0), (8, 16, 1, 0), (46, 3, 0, 0), (10, 200, 1, 0), (4, 1, 1, 0), (6, 90, 0, 0),
                            (4, 20, 0, 128), (6, 0, 1, 104), (2, 7, 0, 64), (8, 30, 1, 8), (16, 40, 0, 200), (2, 95, 1, 256)):
-            tune = dict(vec=vecs[-1] if w == 0 else vecs[(k // 2) % len(vecs)], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0,
+            tune = dict(vec=vecs[-1] if w == 0 else vecs[(k // 2) % len(vecs)], hints=(k // 2) & 1, block=128,
                         pdl=g, graph=g, tb_depth=k, tb_rows=h, tb_cols=w)
             lat.set_tuning(**tune)
             lat.upload(fA, walls)
@@ -196,63 +172,35 @@ def test_every_kernel_variant_is_bit_identical(prec):
             lat.run(2)
             lat.run(c["steps"] - 2)
             _assert_same(lat.download("A"), o.f_view("A"), f"wavefront fA (2 + {c['steps'] - 2} steps) with {tune}")
-        # the same schedules through the dataflow kernel (one launch per macro-step)
-        for n, (k, h, u, extra) in enumerate(((2, 0, 1, {}), (4, 7, 1, dict(block=32)), (8, 16, 2, dict(ctas_per_sm=1)), (46, 3, 1, {}),
-                                              (10, 200, 5, dict(hints=1)), (4, 1, 1, dict(block=64, ctas_per_sm=2)), (6, 90, 64, {}),
-                                              (16, 40, 3, dict(block=256, hints=1)))):
-            tune = dict(dict(vec=vecs[n % len(vecs)], neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=1, graph=0,
-                             tb_depth=k, tb_rows=h, tb_cols=1 << 20, dataflow=u), **extra)
-            lat.set_tuning(**tune)
-            lat.upload(fA, walls)
-            l0 = lat.launches
-            lat.run(c["steps"])
-            _assert_same(lat.download("A"), o.f_view("A"), f"dataflow fA with {tune}")
-            if c["ny"] % (8 if prec == "sp" else 4) == 0 and 2 * k + 2 <= c["nx"]:
-                # prologue (2) + one launch per macro-step: (steps - k) // k full ones, then the last one or two
-                assert lat.launches - l0 <= 2 + -(-c["steps"] // k) + 1, "the dataflow kernel did not run"
-            lat.upload(fA, walls)
-            lat.run(2)
-            lat.run(c["steps"] - 2)
-            _assert_same(lat.download("A"), o.f_view("A"), f"dataflow fA (2 + {c['steps'] - 2} steps) with {tune}")
-        lat.set_tuning(dataflow=0, hints=0)
-        # fused pairs (phase 2 + next phase 1 in one kernel, rims in a second): tile heights around the edge cases
-        for tr, blk, pdl in ((3, 128, 0), (4, 64, 1), (7, 128, 1), (16, 64, 0), (95, 128, 1), (96, 64, 0), (200, 128, 0), (4096, 64, 1)):
-            tune = dict(vec=1, neighbour=1, hints=0, block=blk, ctas_per_sm=0, persistent=0, pdl=pdl, graph=0, tb_depth=0, fuse_rows=tr)
-            lat.set_tuning(**tune)
-            lat.upload(fA, walls)
-            l0 = lat.launches
-            lat.run(c["steps"])
-            _assert_same(lat.download("A"), o.f_view("A"), f"fused pairs fA with {tune}")
-            if c["ny"] % (8 if prec == "sp" else 4) == 0:
-                assert lat.launches - l0 == 2 + 2 + 2 * (c["steps"] // 2 - 1), "the pair kernel did not run"
-            lat.upload(fA, walls)
-            lat.run(2)
-            lat.run(c["steps"] - 2)
-            _assert_same(lat.download("A"), o.f_view("A"), f"fused pairs fA (2 + {c['steps'] - 2} steps) with {tune}")
-        lat.set_tuning(fuse_rows=0)
 
 
-@pytest.mark.skipif(os.environ.get("LBM_TEST_EXPERIMENTAL") != "1",
-                    reason="lbm_tuning.stage_smem (cp.async staging) was written after the round-1 GPU budget was spent and has not run "
-                           "on a GPU yet: set LBM_TEST_EXPERIMENTAL=1 to check it")
 @pytest.mark.parametrize("prec", ["dp", "sp"])
 def test_staged_kernel_is_bit_identical(prec):
+    """The experiment build (latticeboltzmann_b200/exp/, include/lbm_b200_experimental.h): the in-place step with the next
+    row staged in shared memory by cp.async (stage_smem 1) or, for whole-row launches of phase 2, by TMA bulk copies
+    (stage_smem 2).  north_star's "TMA or shared-memory staging": bit-identical, measured slower (profiles/r02_run1)."""
     c = dict(prec=prec, isa="avx", nx=96, ny=520, scene="random", perturb=17, steps=10)
     fA, walls = cases.make_inputs(c)
     o = _oracle(c, fA, walls, c["steps"])
-    with _lattice(c, inplace=True) as lat:
-        for rpt, extra in ((2, {}), (5, dict(tb_depth=4, tb_rows=9)), (3, dict(pdl=1, graph=2)), (96, {}), (7, dict(ctas_per_sm=1, block=64)),
-                           (4, dict(block=256)), (2, dict(tb_depth=4, tb_rows=20, tb_cols=128, pdl=1)), (1000, dict(block=32)),
-                           # 2: phase 2 through TMA bulk copies (whole rows), phase 1 through cp.async
-                           (2, dict(stage_smem=2)), (3, dict(stage_smem=2, tb_depth=4, tb_rows=9, pdl=1)), (96, dict(stage_smem=2, block=64)),
-                           (7, dict(stage_smem=2, block=32, pdl=1, graph=2)), (4, dict(stage_smem=2, tb_depth=4, tb_rows=20, tb_cols=128))):
-            tune = dict(dict(vec=1, neighbour=1, hints=0, block=128, ctas_per_sm=0, persistent=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0,
-                             rows_per_thread=rpt, stage_smem=1), **extra)
+    with _lattice(c, inplace=True, experimental=True) as lat:
+        for rpt, mode, extra in ((2, 1, {}), (5, 1, dict(tb_depth=4, tb_rows=9)), (3, 1, dict(pdl=1, graph=2)), (96, 1, {}), (7, 1, dict(block=64)),
+                                 (4, 1, dict(block=256)), (2, 1, dict(tb_depth=4, tb_rows=20, tb_cols=128, pdl=1)), (1000, 1, dict(block=32)),
+                                 # 2: phase 2 through TMA bulk copies (whole rows), phase 1 through cp.async
+                                 (2, 2, {}), (3, 2, dict(tb_depth=4, tb_rows=9, pdl=1)), (96, 2, dict(block=64)),
+                                 (7, 2, dict(block=32, pdl=1, graph=2)), (4, 2, dict(tb_depth=4, tb_rows=20, tb_cols=128))):
+            tune = dict(dict(vec=1, hints=0, block=128, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0), **extra)
             lat.set_tuning(**tune)
+            lat.set_experimental(stage_smem=mode, rows_per_thread=rpt)
             lat.upload(fA, walls)
+            l0 = lat.launches
             lat.run(4)
             lat.run(c["steps"] - 4)
-            _assert_same(lat.download("A"), o.f_view("A"), f"staged in-place fA with {tune}")
+            _assert_same(lat.download("A"), o.f_view("A"), f"staged in-place fA with {tune}, stage_smem {mode}, rows_per_thread {rpt}")
+            assert lat.launches > l0
+        lat.set_experimental(stage_smem=0, rows_per_thread=0)        # and off again: the product kernels of the same build
+        lat.upload(fA, walls)
+        lat.run(c["steps"])
+        _assert_same(lat.download("A"), o.f_view("A"), "experiment build, staging off")
 
 
 @pytest.mark.parametrize("prec", ["dp", "sp"])
@@ -297,15 +245,45 @@ def test_print_lattice_bytes(tmp_path):
         assert (tmp_path / f"gpu_{prec}.csv").read_bytes() == (tmp_path / f"cpu_{prec}.csv").read_bytes()
 
 
+def test_print_lattice_over_slabs_and_driver_dump(tmp_path):
+    """SAVELATTICE of a multi-slab run (LB.c:155-159): lbm_print_lattice_group writes ONE file for the whole lattice, identical
+    to the single-slab file; the C driver's DUMP_EVERY writes data/<step>.csv at the reference's observation points."""
+    from latticeboltzmann_b200 import Lattice, group_run, make_ring, print_lattice_group
+    nx, ny = 230, 120
+    with Lattice(nx, ny, "dp") as lat:
+        lat.InitializeArrays()
+        lat.run(40)
+        lat.PrintLattice(tmp_path / "one.csv")
+    for inplace in (False, True):
+        slabs = make_ring(nx, ny, 3, "dp", inplace=inplace)
+        try:
+            for s in slabs:
+                s.InitializeArrays()
+            group_run(slabs, 40)
+            print_lattice_group(slabs, tmp_path / "ring.csv")
+        finally:
+            for s in slabs:
+                s.close()
+        assert (tmp_path / "ring.csv").read_bytes() == (tmp_path / "one.csv").read_bytes()
+    (tmp_path / "data").mkdir()
+    exe = os.path.join(ROOT, "driver", "lbm_b200_dp")
+    out = subprocess.run([exe, str(nx), str(ny), "80", "1", "0", "20"], capture_output=True, text=True, timeout=300, cwd=tmp_path)
+    assert out.returncode == 0, out.stderr
+    assert sorted(os.listdir(tmp_path / "data")) == ["0.csv", "20.csv", "40.csv", "60.csv"]
+    assert (tmp_path / "data" / "40.csv").read_bytes() == (tmp_path / "one.csv").read_bytes()
+    out = subprocess.run([exe, str(nx), str(ny), "80", "1", "0", "5"], capture_output=True, text=True, timeout=300, cwd=tmp_path)   # odd: every 10
+    assert out.returncode == 0 and "70.csv" in os.listdir(tmp_path / "data") and "5.csv" not in os.listdir(tmp_path / "data")
+
+
 def test_error_behaviour():
     from latticeboltzmann_b200 import Lattice, LbmError
     with Lattice(8, 16) as lat:
         with pytest.raises(LbmError):
             lat.run(2)                                   # nothing loaded
         f, w = np.zeros((9, 8, 16)), np.zeros((8, 16), dtype=np.int8)
-        w[3, 3] = 2
+        w[3, 3] = 4
         with pytest.raises(LbmError):
-            lat.upload(f + 0.1, w)                       # mask must be 0/1
+            lat.upload(f + 0.1, w)                       # mask values: 0 fluid, 1 bounce-back, 2 / 3 reflect
         w[3, 3] = 1
         lat.upload(f + 0.1, w)
         with pytest.raises(LbmError):

@@ -127,11 +127,11 @@ def test_fused_pairs_leave_what_two_phases_leave(nx, ny, tile_rows, tile_cols):
 # the wavefront (temporal blocking) schedule with the in-place phases: the library's own launch list, sites of a
 # launch in any order -- every read must find the label of the step before, although neighbouring tiles are
 # several steps apart (the claim behind DESIGN.md "temporal blocking": read-after-write dependencies only)
-@pytest.mark.parametrize("nx,ny,depth,rows,cols,dataflow", [(24, 144, 8, 5, 16, False), (33, 136, 4, 9, 64, False), (11, 64, 4, 2, 0, False),
-                                                            (40, 64, 6, 7, 0, False), (40, 64, 6, 7, 1 << 20, True), (14, 40, 6, 2, 1 << 20, True)])
-def test_wavefront_schedule_with_in_place_phases(nx, ny, depth, rows, cols, dataflow):
+@pytest.mark.parametrize("nx,ny,depth,rows,cols", [(24, 144, 8, 5, 16), (33, 136, 4, 9, 64), (11, 64, 4, 2, 0),
+                                                   (40, 64, 6, 7, 0), (40, 64, 6, 7, 1 << 20), (14, 40, 6, 2, 1 << 20)])
+def test_wavefront_schedule_with_in_place_phases(nx, ny, depth, rows, cols):
     from latticeboltzmann_b200.solver import tb_schedule
-    k, launches = tb_schedule(nx, ny, depth, rows, cols, "dp", dataflow=dataflow)
+    k, launches = tb_schedule(nx, ny, depth, rows, cols, "dp")
     assert k >= 2
     m = Model(nx, ny)
     rng = np.random.default_rng(nx + ny + depth)

@@ -72,6 +72,28 @@ def test_oracle_matches_compiled_reference(prec, isa):
     assert r.reynolds() == o.reynolds()
 
 
+@pytest.mark.skipif(not ref_available(), reason="oracle/_ref not built (reference checkout absent)")
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+def test_oracle_print_lattice_matches_compiled_reference(prec, tmp_path, monkeypatch):
+    """PrintLattice (LB.c:610-639) of the reference itself, byte for byte: pins the CSV leg of the oracle, which is what
+    lbm_print_lattice is compared with on the GPU (tests/test_gpu_parity.py::test_print_lattice_bytes)."""
+    nx, ny = 231, 133
+    r, o = Ref(prec, nx, ny, "avx"), Oracle(prec, nx, ny, VECWIDTH[(prec, "avx")])
+    r.initialize()
+    o.initialize()
+    r.run(40)
+    o.run(40)
+    (tmp_path / "data").mkdir()
+    monkeypatch.chdir(tmp_path)                       # the reference writes data/<step>.csv relative to the cwd (LB.c:613)
+    r.print_lattice(40)
+    assert o.print_lattice(str(tmp_path / "oracle.csv")) == 0
+    ref_bytes = (tmp_path / "data" / "40.csv").read_bytes()
+    assert len(ref_bytes) > nx * ny * 12 and ref_bytes.count(b"\n") == nx
+    assert (tmp_path / "oracle.csv").read_bytes() == ref_bytes
+    rho, ux, uy = o.macroscopic()
+    assert np.any(ux * ux + uy * uy > 0)            # the file is not all zeros
+
+
 def test_known_answer_reynolds_10k():
     """The reference's only printed physics number (LB.c:173) after the shipped 10,000 steps,
     400x2000: strict -O2 AVX builds, measured with the compiled reference."""

@@ -147,62 +147,6 @@ def test_slab_ring_event_protocol(heights, ny, depth, rows, cols, seed):
 
 
 # ---------------------------------------------------------------------------------------------------
-# dataflow kernel (lbm_tuning.dataflow): one launch per macro-step.  Its item order must be a valid launch
-# order too, and its execution model -- G co-resident CTAs, CTA g takes items g, g+G, ... in that order,
-# an item of level s waits until the per-row counters of rows i-1, i, i+1 at level s-1 are full -- must
-# neither deadlock nor run an item early, whatever the interleaving.
-# ---------------------------------------------------------------------------------------------------
-DATAFLOW = [(400, 4000, 16, 0), (96, 520, 4, 20), (96, 520, 46, 3), (40, 1024, 8, 12), (11, 64, 4, 2), (10, 64, 4, 0),
-            (7, 40, 2, 0), (6, 40, 2, 5), (401, 1000, 32, 37), (66, 64, 32, 2)]
-
-
-@pytest.mark.parametrize("prec", ["dp", "sp"])
-@pytest.mark.parametrize("nx,ny,depth,rows", DATAFLOW)
-def test_dataflow_order_is_a_valid_launch_order(nx, ny, depth, rows, prec):
-    k, plain = tb_schedule(nx, ny, depth, rows, ny, prec)
-    k2, launches = tb_schedule(nx, ny, depth, rows, ny, prec, dataflow=True)
-    assert k2 == k and sorted(launches) == sorted(plain)            # the same launches, reordered
-    _check(nx, ny, k, launches)
-
-
-@pytest.mark.parametrize("nx,ny,depth,rows,chunks,ctas", [(96, 520, 4, 20, 3, 7), (40, 1024, 8, 12, 2, 64), (11, 64, 4, 2, 1, 5),
-                                                          (66, 64, 32, 2, 1, 1), (66, 64, 32, 2, 2, 1000), (7, 40, 2, 0, 4, 3)])
-def test_dataflow_execution_model(nx, ny, depth, rows, chunks, ctas):
-    k, launches = tb_schedule(nx, ny, depth, rows, ny, "dp", dataflow=True)
-    assert k >= 2
-    items = [(s, (r0 + rr) % nx, ch) for s, r0, r1, _, _ in launches for rr in range(r1 - r0) for ch in range(chunks)]
-    assert len(items) == k * nx * chunks
-    rng = np.random.default_rng(nx * 1000 + ctas)
-    cnt = np.zeros((k, nx), dtype=np.int32)                         # the kernel's counters
-    level = np.zeros((nx, chunks), dtype=np.int32)                  # model: levels completed per (row, column chunk)
-    nxt = list(range(min(ctas, len(items))))
-    left = len(items)
-    while left:
-        ready = []
-        for g, n in enumerate(nxt):
-            if n >= len(items):
-                continue
-            s, r, _ = items[n]
-            if s == 0 or all(cnt[s - 1, (r + d) % nx] == chunks for d in (-1, 0, 1)):
-                ready.append(g)
-        assert ready, "deadlock: every CTA waits"
-        g = int(rng.choice(ready))
-        s, r, ch = items[nxt[g]]
-        assert level[r, ch] == s
-        for d in (-1, 0, 1):                                        # what the item reads was written by level s-1 ...
-            for e in (-1, 0, 1):
-                assert level[(r + d) % nx, (ch + e) % chunks] >= s
-        # ... and nothing it overwrites is still needed by a level-(s-1) item: those read rows within +-1 of their own,
-        # all of which are done (checked above for rows r-1..r+1; rows r+-2 never read row r's level-(s-1) slots that
-        # this item rewrites -- DESIGN.md "in-place streaming": phase 1 touches rows i-1..i+1, phase 2 row i only)
-        level[r, ch] = s + 1
-        cnt[s, r] += 1
-        nxt[g] += len(nxt)
-        left -= 1
-    assert (level == k).all() and (cnt == chunks).all()
-
-
-# ---------------------------------------------------------------------------------------------------
 # BASELINE.json's full sizes: the 2-D site model above would need gigabytes, but the schedule is a product of two
 # 1-D schedules (column pieces outermost, row pieces next, levels innermost), so it is enough that (i) the launch
 # list really is that product and (ii) each axis' own piece order respects the 1-D dependencies (reach 1).

@@ -23,7 +23,7 @@ def timeit(lat, phase, nx, n=1500):
 
 out = []
 for prec, nx, ny in (("dp", 400, 2000), ("sp", 400, 4000)):
-    with Lattice(nx, ny, prec, inplace=True) as lat:
+    with Lattice(nx, ny, prec, inplace=True, experimental=True) as lat:
         lat.InitializeArrays()
         lat.run(10)
         combos = [dict(vec=1, rows_per_thread=0, stage_smem=0, block=128)]
@@ -36,7 +36,8 @@ for prec, nx, ny in (("dp", 400, 2000), ("sp", 400, 4000)):
             for rpt in (4, 8, 16, 32):
                 combos.append(dict(vec=1, rows_per_thread=rpt, stage_smem=2, block=blk))
         for cmb in combos:
-            lat.set_tuning(pdl=1, graph=0, tb_depth=0, neighbour=1, **cmb)
+            lat.set_tuning(pdl=1, graph=0, tb_depth=0, vec=cmb['vec'], block=cmb['block'])
+            lat.set_experimental(stage_smem=cmb['stage_smem'], rows_per_thread=cmb['rows_per_thread'])
             for phase in (0, 1):
                 if cmb["stage_smem"] == 2 and phase == 0:
                     continue

@@ -12,7 +12,7 @@ from latticeboltzmann_b200 import Lattice  # noqa: E402
 
 out = []
 for prec, nx, ny, T in (("dp", 400, 2000, 4000), ("dp", 400, 4000, 2000), ("sp", 400, 4000, 2000), ("dp", 8192, 32768, 48)):
-    with Lattice(nx, ny, prec, inplace=True) as lat:
+    with Lattice(nx, ny, prec, inplace=True, experimental=True) as lat:
         def init():
             if nx <= 2000:
                 lat.InitializeArrays()
@@ -27,7 +27,8 @@ for prec, nx, ny, T in (("dp", 400, 2000, 4000), ("dp", 400, 4000, 2000), ("sp",
         init(); lat.run(32); want = lat.download("A")
         for mode, blk in ((1, 128), (1, 256), (2, 128), (2, 64)):     # 1: cp.async both phases; 2: TMA bulk copies in phase 2
             for rpt in (4, 8, 16):
-                lat.set_tuning(vec=1, rows_per_thread=rpt, stage_smem=mode, block=blk)
+                lat.set_tuning(vec=1, block=blk)
+                lat.set_experimental(stage_smem=mode, rows_per_thread=rpt)
                 init(); lat.run(32)
                 same = bool(np.array_equal(lat.download("A").view(np.uint8), want.view(np.uint8)))
                 lat.run_timed(min(T, 400))
