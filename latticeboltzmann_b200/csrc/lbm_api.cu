@@ -230,12 +230,16 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (e == cudaSuccess) e = cudaMalloc(&c->mask, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMalloc(&c->flags, 4 * sizeof(int));
 	if (e == cudaSuccess) e = cudaMalloc(&c->slip, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t));
-	if (e == cudaSuccess) e = cudaMemset(c->f[0], 0, fbytes);
-	if (e == cudaSuccess && c->f[1]) e = cudaMemset(c->f[1], 0, fbytes);
-	if (e == cudaSuccess) e = cudaMemset(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
-	if (e == cudaSuccess) e = cudaMemset(c->slip, 0, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t));
-	if (e == cudaSuccess) e = cudaMemset(c->flags, 0, 4 * sizeof(int));
 	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaStreamCreateWithFlags(&c->stream[k], cudaStreamNonBlocking);
+	/* Zero everything ON THE CONTEXT'S OWN STREAM and wait: the streams are non-blocking, so a cudaMemset on the legacy
+	 * default stream is not ordered with them -- on a 19 GB lattice it was still running when lbm_initialize_arrays'
+	 * kernels had finished, and wiped the wall mask they wrote (found by the cross-engine checksum at 8192x32768). */
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->f[0], 0, fbytes, c->stream[0]);
+	if (e == cudaSuccess && c->f[1]) e = cudaMemsetAsync(c->f[1], 0, fbytes, c->stream[0]);
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t), c->stream[0]);
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->slip, 0, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t), c->stream[0]);
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->flags, 0, 4 * sizeof(int), c->stream[0]);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream[0]);
 	if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming);
 	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&c->ev_bnd[k], cudaEventDisableTiming);
 	if (e == cudaSuccess) e = cudaEventCreate(&c->ev_t0);
@@ -1322,7 +1326,8 @@ int lbm_ipc_connect(lbm_ctx *c, const unsigned char up[LBM_IPC_BLOB_BYTES], cons
 	c->dn = peer[1];
 	c->sync_mode = SYNC_FLAGS;
 	c->epoch = 0;
-	CK(cudaMemset(c->flags, 0, 4 * sizeof(int)));
+	CK(cudaMemsetAsync(c->flags, 0, 4 * sizeof(int), c->stream[0]));
+	CK(cudaStreamSynchronize(c->stream[0]));
 	return LBM_OK;
 }
 

@@ -83,7 +83,7 @@ class Oracle(_Base):
     class Params(ctypes.Structure):
         pass
 
-    def __init__(self, prec, nx, ny, vw=None, source_col=0, **kw):
+    def __init__(self, prec, nx, ny, vw=None, source_col=0, outflow=False, **kw):
         vw = VECWIDTH[(prec, "avx")] if vw is None else vw
         super().__init__(prec, nx, ny, vw, **kw)
         path = os.path.join(HERE, f"liblbm_oracle_{prec}.so")
@@ -94,8 +94,9 @@ class Oracle(_Base):
 
         class P(ctypes.Structure):
             _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int), ("ldy", ctypes.c_int),
-                        ("vw", ctypes.c_int), ("tau", real), ("accel", real), ("rho0", real), ("source_col", ctypes.c_int)]
-        self.p = P(self.nx, self.ny, self.ldy, self.vw, self.tau, self.accel, self.rho0, int(source_col))
+                        ("vw", ctypes.c_int), ("tau", real), ("accel", real), ("rho0", real), ("source_col", ctypes.c_int),
+                        ("outflow", ctypes.c_int)]
+        self.p = P(self.nx, self.ny, self.ldy, self.vw, self.tau, self.accel, self.rho0, int(source_col), int(bool(outflow)))
         self.lib.lbo_compute_reynolds.restype = real
         assert self.lib.lbo_sizeof_real() == np.dtype(self.dtype).itemsize
 

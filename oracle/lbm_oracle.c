@@ -45,6 +45,10 @@ static const int PULL_DI[Q] = { 0, 0, -1, 0, +1, -1, -1, +1, +1 };
 static const int PULL_DJ[Q] = { 0, -1, 0, +1, 0, -1, +1, +1, -1 };
 /* bounce-back partner: dst[s] = pulled[OPP[s]]; LB.c:247-254 */
 static const int OPP[Q] = { 0, 3, 4, 1, 2, 7, 8, 5, 6 };
+/* "reflect (slip)" walls -- named at LB.c:21, not implemented by the reference; defined in include/lbm_b200.h (wall
+ * values 2 and 3): specular reflection about a wall whose normal is x (dx -> -dx) or y (dy -> -dy).  Parity unpinned. */
+static const int MIRROR_X[Q] = { 0, 1, 4, 3, 2, 8, 7, 6, 5 };
+static const int MIRROR_Y[Q] = { 0, 3, 2, 1, 4, 6, 5, 8, 7 };
 
 typedef struct {
 	int nx, ny;      /* lattice rows (x, slow) and columns (y, contiguous) */
@@ -53,6 +57,10 @@ typedef struct {
 	real tau, accel, rho0;
 	int source_col;  /* column ApplySource acts on: 0 in the reference (LB.c:500-515).  Test windows cut out of a larger
 	                    lattice (tests/test_gpu_fullsize.py) put the lattice's column 0 elsewhere, or nowhere (-1). */
+	int outflow;     /* 0: y wraps (the reference, LB.c:233-234).  1: open y ends -- the option the reference's dead
+	                    WRAPAROUND macro names (LB.c:42-43) and never implements; defined in include/lbm_b200.h
+	                    (LBM_Y_OUTFLOW): what would be pulled from beyond an end column comes from that end column
+	                    itself.  NOT pinned against the reference (it has no such code): parity unpinned. */
 } lbo_params;
 
 int lbo_sizeof_real(void) { return (int)sizeof(real); }
@@ -77,7 +85,11 @@ static void weights(real w[Q])
 static inline void pull(const lbo_params *p, const real *src, int i, int j, real f[Q])
 {
 	const int up = (i + 1) % p->nx, dn = i ? i - 1 : p->nx - 1;   /* LB.c:231-232 */
-	const int rt = (j + 1) % p->ny, lf = j ? j - 1 : p->ny - 1;   /* LB.c:233-234 */
+	int rt = (j + 1) % p->ny, lf = j ? j - 1 : p->ny - 1;         /* LB.c:233-234 */
+	if (p->outflow) {                                             /* open ends: the end column itself */
+		if (j == p->ny - 1) rt = j;
+		if (j == 0) lf = j;
+	}
 	for (int s = 0; s < Q; s++) {
 		const int ii = PULL_DI[s] < 0 ? dn : PULL_DI[s] > 0 ? up : i;
 		const int jj = PULL_DJ[s] < 0 ? lf : PULL_DJ[s] > 0 ? rt : j;
@@ -85,10 +97,12 @@ static inline void pull(const lbo_params *p, const real *src, int i, int j, real
 	}
 }
 
-static inline void bounce(const lbo_params *p, real *dst, int i, int j, const real f[Q])
+/* wall site: kind 1 bounces back (LB.c:246-255); 2 / 3 reflect (see MIRROR_X / MIRROR_Y) */
+static inline void bounce(const lbo_params *p, real *dst, int i, int j, const real f[Q], int kind)
 {
+	const int *perm = kind == 2 ? MIRROR_X : kind == 3 ? MIRROR_Y : OPP;
 	for (int s = 1; s < Q; s++)            /* speed 0 is NOT written at walls */
-		dst[at(p, s, i, j)] = f[OPP[s]];
+		dst[at(p, s, i, j)] = f[perm[s]];
 }
 
 /*
@@ -165,7 +179,7 @@ static void collide_group(const lbo_params *p, const real *src, real *dst,
 			for (int s = 0; s < Q; s++)
 				dst[at(p, s, i, j + k)] = relax_double(f[k][s], feq[k][s], p->tau);
 		} else {
-			bounce(p, dst, i, j + k, f[k]);                    /* LB.c:466-475 */
+			bounce(p, dst, i, j + k, f[k], walls[(size_t)i * p->ldy + j + k]);   /* LB.c:466-475 */
 		}
 	}
 }
@@ -176,8 +190,8 @@ static void collide_scalar(const lbo_params *p, const real *src, real *dst,
 {
 	real f[Q];
 	pull(p, src, i, j, f);
-	if (walls[(size_t)i * p->ldy + j] == 1) {                  /* LB.c:246 */
-		bounce(p, dst, i, j, f);
+	if (walls[(size_t)i * p->ldy + j] != 0) {                  /* LB.c:246 (== 1 there; 2, 3: the reflect walls) */
+		bounce(p, dst, i, j, f, walls[(size_t)i * p->ldy + j]);
 		return;
 	}
 	real rho = R(0.0);

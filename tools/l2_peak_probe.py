@@ -17,7 +17,7 @@ import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-MODES = {0: "read", 1: "copy", 2: "update", 3: "read4", 4: "update4", 5: "update8"}
+MODES = {0: "read", 1: "copy", 2: "update", 3: "read4", 4: "update4", 5: "update8", 6: "update4_persistent"}
 
 
 def load_probe():
@@ -56,11 +56,11 @@ def main():
     lib = load_probe()
     res = {"kernels": [], "lbm": []}
     for mb in (8, 16, 24, 32, 40, 48, 56, 64, 80, 96, 128, 256, 512):
-        for mode in (0, 1, 2, 3, 4, 5):
+        for mode in (0, 1, 2, 3, 4, 5, 6):
             best = None
             for block, cps in ((256, 0), (128, 0), (512, 0), (256, 8), (1024, 2)):
                 g = ctypes.c_double()
-                rc = lib.l2probe(int(mb * 1e6), mode, block, cps, 200 if mb <= 128 else 40, ctypes.byref(g))
+                rc = lib.l2probe(int(mb * 1e6), mode, block, cps, (200 if mb <= 128 else 40) // (10 if mode == 6 else 1), ctypes.byref(g))
                 if rc == 0 and (best is None or g.value > best["gbs"]):
                     best = {"working_set_mb": mb, "mode": MODES[mode], "gbs": round(g.value, 1), "block": block, "ctas_per_sm": cps}
             res["kernels"].append(best)

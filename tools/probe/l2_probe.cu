@@ -3,6 +3,7 @@
 //   mode 0  read      sum of the buffer                         bytes = size
 //   mode 1  copy      b[i] = a[i]          (two buffers)        bytes = 2 * size/2 ... reported as read + write
 //   mode 3  read, 4 loads in flight per thread;  mode 4 / 5  update with 4 / 8 loads in flight per thread
+//   mode 6  update, 4 loads in flight, 10 sweeps per launch by one resident wave of CTAs (no ramp / drain between sweeps)
 //   mode 2  update    a[i] = a[i] * c + d  (in place)           bytes = read + write of the same lines -- the access
 //                                                               shape of the in-place LBM phases (9 loads + 9 stores per site)
 // 128-bit accesses, one element per thread and pass, back-to-back launches timed with CUDA events.
@@ -46,6 +47,24 @@ __global__ void k_update_u(double2 *a, size_t n)
 		for (int u = 0; u < U; u++) a[base + threadIdx.x + (size_t)u * blockDim.x] = v[u];
 	}
 }
+// the same, `passes` sweeps over the buffer inside ONE launch (a thread revisits its own elements each pass, so passes of
+// different CTAs may overlap freely): no ramp / drain between sweeps, as the library's step kernels avoid with programmatic
+// dependent launch
+template <int U>
+__global__ void k_update_p(double2 *a, size_t n, int passes)
+{
+	const size_t chunk = (size_t)U * blockDim.x;
+	for (int pass = 0; pass < passes; pass++)
+		for (size_t base = (size_t)blockIdx.x * chunk; base + chunk <= n; base += (size_t)gridDim.x * chunk) {
+			double2 v[U];
+#pragma unroll
+			for (int u = 0; u < U; u++) v[u] = a[base + threadIdx.x + (size_t)u * blockDim.x];
+#pragma unroll
+			for (int u = 0; u < U; u++) { v[u].x = v[u].x * 0.999999 + 1e-9; v[u].y = v[u].y * 0.999999 + 1e-9; }
+#pragma unroll
+			for (int u = 0; u < U; u++) a[base + threadIdx.x + (size_t)u * blockDim.x] = v[u];
+		}
+}
 template <int U>
 __global__ void k_read_u(const double2 *a, size_t n, double *sink)
 {
@@ -69,7 +88,8 @@ static void launch(int mode, size_t grid, int block, double2 *a, double2 *b, siz
 	case 2: k_update<<<(unsigned)grid, block>>>(a, n); break;
 	case 3: k_read_u<4><<<(unsigned)grid, block>>>(a, n, sink); break;
 	case 4: k_update_u<4><<<(unsigned)grid, block>>>(a, n); break;
-	default: k_update_u<8><<<(unsigned)grid, block>>>(a, n); break;
+	case 5: k_update_u<8><<<(unsigned)grid, block>>>(a, n); break;
+	default: k_update_p<4><<<(unsigned)grid, block>>>(a, n, 10); break;   /* mode 6: 10 sweeps per launch */
 	}
 }
 
@@ -87,6 +107,7 @@ extern "C" int l2probe(size_t bytes, int mode, int block, int ctas_per_sm, int r
 	cudaMemset(a, 0, n * sizeof(double2));
 	size_t grid = (n + block - 1) / block;
 	if (mode >= 3) grid = (n + (size_t)block * (mode == 5 ? 8 : 4) - 1) / ((size_t)block * (mode == 5 ? 8 : 4));
+	if (mode == 6 && ctas_per_sm <= 0) ctas_per_sm = 2048 / block;       /* persistent: one resident wave */
 	if (ctas_per_sm > 0 && grid > (size_t)sms * ctas_per_sm) grid = (size_t)sms * ctas_per_sm;
 	cudaEvent_t e0, e1;
 	cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -106,7 +127,7 @@ extern "C" int l2probe(size_t bytes, int mode, int block, int ctas_per_sm, int r
 		cudaEventElapsedTime(&ms, e0, e1);
 		if (ms < best) best = ms;
 	}
-	const double moved = ((mode == 0 || mode == 3) ? 1.0 : 2.0) * (double)n * sizeof(double2) * reps;
+	const double moved = ((mode == 0 || mode == 3) ? 1.0 : 2.0) * (double)n * sizeof(double2) * reps * (mode == 6 ? 10 : 1);
 	*gbs = moved / (best * 1e-3) / 1e9;
 	cudaFree(a); if (b) cudaFree(b); cudaFree(sink);
 	cudaEventDestroy(e0); cudaEventDestroy(e1);
