@@ -217,7 +217,7 @@ int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary strea
  * pipelining, capped grids: all slower than the defaults, numbers in DESIGN.md / profiles/) is no longer here; the
  * shared-memory staged kernels (cp.async / TMA) live in the experiment build only (include/lbm_b200_experimental.h). */
 typedef struct {
-	int vec;          /* sites per thread: 1,2,4 (8 SP); 0 = by lattice size (DP: 1 up to 16 Mi sites and in place, else 4; SP: 4) */
+	int vec;          /* sites per thread: 1, 2 or 4; 0 = by lattice size (DP: 1 up to 16 Mi sites and in place, else 4; SP: 4) */
 	int block;        /* threads per CTA; 0 = default 128 (the SP in-place kernels run at most 256) */
 	int hints;        /* 1: A/B kernel: L1::no_allocate loads + streaming stores; in-place kernels under temporal blocking: the LAST
 	                     level of a macro-step stores with the evict-first policy (its results are not read again while the tile

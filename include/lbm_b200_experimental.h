@@ -19,6 +19,8 @@ extern "C" {
 typedef struct {
 	int stage_smem;       /* 0 off; 1 = cp.async staging in both phases; 2 = phase 2 by TMA bulk copies (phase 1: cp.async) */
 	int rows_per_thread;  /* >= 2: rows each thread walks (the staging pipelines over them); vec must be 1 */
+	int smem_pad;         /* bytes of (unused) dynamic shared memory requested by every in-place step launch: caps the CTAs
+	                         resident per SM -- the residency probe (a CTA's lifetime is what one launch loses at its drain) */
 } lbm_experimental;
 int lbm_set_experimental(lbm_ctx *ctx, const lbm_experimental *x);
 #ifdef __cplusplus

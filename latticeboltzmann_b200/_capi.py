@@ -47,7 +47,7 @@ def _structs(real):
                     ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int), ("tb_cols", ctypes.c_int)]
 
     class Experimental(ctypes.Structure):      # include/lbm_b200_experimental.h (experiment build only)
-        _fields_ = [("stage_smem", ctypes.c_int), ("rows_per_thread", ctypes.c_int)]
+        _fields_ = [("stage_smem", ctypes.c_int), ("rows_per_thread", ctypes.c_int), ("smem_pad", ctypes.c_int)]
 
     return Config, Scene, SlabInfo, Tuning, Experimental
 

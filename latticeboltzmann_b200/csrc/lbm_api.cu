@@ -87,6 +87,7 @@ struct lbm_ctx {
 	int has_state;
 	real_t w0, w14, w58, itau, a14, a58;
 	double itau_d;
+	unsigned *seam_done;         // device counter of the fused seam barrier (CTAs of the running seam launch that have finished)
 	uint32_t *slip;              // device [2][nxl][ldw]: "reflect" walls with normal x / normal y (mask values 2 / 3)
 	int has_slip;                // any bit set in `slip` (else the kernels are told there is none)
 	int outflow;                 // lbm_config.boundary_y
@@ -146,6 +147,8 @@ StepParams<real_t> make_params(const lbm_ctx *c, int src, int r0, int r1, int ta
 	p.tail_source = tail_source;
 	p.outflow = c->outflow;
 	p.slip = c->has_slip ? c->slip : nullptr;
+	p.seam_flags = nullptr; p.seam_up = p.seam_dn = nullptr; p.seam_done = nullptr;
+	p.seam_wait = p.seam_signal = 0; p.seam_timeout_ns = 0;
 	p.w0 = c->w0; p.w14 = c->w14; p.w58 = c->w58;
 	p.itau = c->itau; p.itau_d = c->itau_d;
 	p.a14 = c->a14; p.a58 = c->a58;
@@ -229,6 +232,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (e == cudaSuccess && !c->inplace) e = cudaMalloc(&c->f[1], fbytes);
 	if (e == cudaSuccess) e = cudaMalloc(&c->mask, (size_t)c->nxl * c->ldw * sizeof(uint32_t));
 	if (e == cudaSuccess) e = cudaMalloc(&c->flags, 4 * sizeof(int));
+	if (e == cudaSuccess) e = cudaMalloc(&c->seam_done, sizeof(unsigned));
 	if (e == cudaSuccess) e = cudaMalloc(&c->slip, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t));
 	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaStreamCreateWithFlags(&c->stream[k], cudaStreamNonBlocking);
 	/* Zero everything ON THE CONTEXT'S OWN STREAM and wait: the streams are non-blocking, so a cudaMemset on the legacy
@@ -239,6 +243,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (e == cudaSuccess) e = cudaMemsetAsync(c->mask, 0, (size_t)c->nxl * c->ldw * sizeof(uint32_t), c->stream[0]);
 	if (e == cudaSuccess) e = cudaMemsetAsync(c->slip, 0, (size_t)2 * c->nxl * c->ldw * sizeof(uint32_t), c->stream[0]);
 	if (e == cudaSuccess) e = cudaMemsetAsync(c->flags, 0, 4 * sizeof(int), c->stream[0]);
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->seam_done, 0, sizeof(unsigned), c->stream[0]);
 	if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream[0]);
 	if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming);
 	for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&c->ev_bnd[k], cudaEventDisableTiming);
@@ -307,6 +312,7 @@ int lbm_destroy(lbm_ctx *c)
 	drop_graph(c);
 	if (c->flags) cudaFree(c->flags);
 	if (c->slip) cudaFree(c->slip);
+	if (c->seam_done) cudaFree(c->seam_done);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
 	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
 	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -336,13 +342,19 @@ cudaError_t launch_kernel(step_kernel_t kern, const StepParams<real_t> &p, dim3 
 
 /* in-place (AA) step kernels: phase 1 (from the reference layout) / phase 2 (back to it); hint 1 = streaming stores */
 template <int V>
-cudaError_t launch_aa_v(int phase, int hint, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl)
+cudaError_t launch_aa_v(int phase, int hint, const StepParams<real_t> &p, dim3 grid, unsigned block, cudaStream_t st, int pdl, size_t smem = 0)
 {
-	if (hint)
-		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 1>, p, grid, block, st, pdl)
-		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 1>, p, grid, block, st, pdl);
-	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 0>, p, grid, block, st, pdl)
-	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 0>, p, grid, block, st, pdl);
+	if (p.seam_flags)                                            /* a slab's seam launch: carries the neighbour barrier, default eviction priority */
+		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 0, true>, p, grid, block, st, pdl, smem)
+		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 0, true>, p, grid, block, st, pdl, smem);
+	if (hint == 1)
+		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 1>, p, grid, block, st, pdl, smem)
+		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 1>, p, grid, block, st, pdl, smem);
+	if (hint == 2)
+		return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 2>, p, grid, block, st, pdl, smem)
+		                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 2>, p, grid, block, st, pdl, smem);
+	return phase == 1 ? launch_kernel(stream_collide_aa_kernel<real_t, V, 1, 0>, p, grid, block, st, pdl, smem)
+	                  : launch_kernel(stream_collide_aa_kernel<real_t, V, 2, 0>, p, grid, block, st, pdl, smem);
 }
 
 template <int V>
@@ -387,10 +399,35 @@ cudaError_t launch_staged(lbm_ctx *c, int phase, const StepParams<real_t> &p, un
 // jc0 < jc1: restrict the launch to columns [jc0, jc1) (multiples of 8, jc1 may exceed ny and wraps) -- only the
 // in-place vector kernel takes a column range (2-D temporal blocking; needs nyvec == ny)
 // stream_out: in-place kernels store with the evict-first policy (lbm_tuning.hints on the last level of a macro-step)
-int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st, int jc0 = 0, int jc1 = 0, int stream_out = 0)
+/* L2 eviction priority of level s of a macro-step of kk levels (lbm_tuning.hints: bit 0 = the last level stores evict-first,
+ * bit 1 = the other levels load and store evict-last) */
+int tb_hint(const lbm_ctx *c, int s, int kk)
+{
+	if (s == kk - 1) return (c->tune.hints & 1) ? 1 : 0;
+	return (c->tune.hints & 2) ? 2 : 0;
+}
+
+/* the in-place vector kernel can carry a slab's neighbour barrier itself (wait at its start, announce at its end) when it is
+ * the only kernel of the step */
+bool seam_fusable(const lbm_ctx *c)
+{
+	bool ok = c->sync_mode == SYNC_FLAGS && c->inplace && c->vw > 1 && c->nyvec == c->ny;
+#ifdef LBM_EXPERIMENTAL
+	ok = ok && !c->exp.stage_smem;
+#endif
+	return ok;
+}
+
+int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream_t st, int jc0 = 0, int jc1 = 0, int stream_out = 0, int seam = 0)
 {
 	if (r1 <= r0) return LBM_OK;
 	StepParams<real_t> p = make_params(c, src, r0, r1, tail_source);
+	if (seam) {                                                  /* wait for epoch, then announce epoch + 1 (launch_wait / launch_signal in one) */
+		if (!seam_fusable(c)) return fail(LBM_ERR_STATE, "launch_step: this step cannot carry the neighbour barrier");
+		p.seam_flags = c->flags; p.seam_wait = c->epoch;
+		p.seam_up = c->up.flags + 0; p.seam_dn = c->dn.flags + 1; p.seam_signal = ++c->epoch;
+		p.seam_done = c->seam_done; p.seam_timeout_ns = c->wait_timeout_ns;
+	}
 	const unsigned rows = (unsigned)(r1 - r0);
 	int jtail = 0;
 	unsigned ncols = (unsigned)c->nyvec;
@@ -415,13 +452,14 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			if (e == cudaErrorNotYetImplemented) {
 				/* x: the vectors of one row; y: rows (grid-stride above the 65535 limit) */
 				const dim3 g2((ncols / (unsigned)V + block - 1) / block, rows > 65535u ? 65535u : rows);
-				switch (V) {
-				case 1: e = launch_aa_v<1>(phase, stream_out, p, g2, block, st, pdl); break;
-				case 2: e = launch_aa_v<2>(phase, stream_out, p, g2, block, st, pdl); break;
-				case 4: e = launch_aa_v<4>(phase, stream_out, p, g2, block, st, pdl); break;
-#ifdef LBM_FLOAT
-				case 8: e = launch_aa_v<8>(phase, stream_out, p, g2, block, st, pdl); break;
+				size_t pad = 0;
+#ifdef LBM_EXPERIMENTAL
+				pad = (size_t)c->exp.smem_pad;
 #endif
+				switch (V) {
+				case 1: e = launch_aa_v<1>(phase, stream_out, p, g2, block, st, pdl, pad); break;
+				case 2: e = launch_aa_v<2>(phase, stream_out, p, g2, block, st, pdl, pad); break;
+				case 4: e = launch_aa_v<4>(phase, stream_out, p, g2, block, st, pdl, pad); break;
 				default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 				}
 			}
@@ -429,12 +467,9 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 			const unsigned long long total = (unsigned long long)rows * (unsigned)(c->nyvec / V);
 			const unsigned grid = (unsigned)((total + block - 1) / block);
 			switch (V) {
-			case 1: e = launch_vec_v<1>(c->tune.hints, p, grid, block, st, pdl); break;
-			case 2: e = launch_vec_v<2>(c->tune.hints, p, grid, block, st, pdl); break;
-			case 4: e = launch_vec_v<4>(c->tune.hints, p, grid, block, st, pdl); break;
-#ifdef LBM_FLOAT
-			case 8: e = launch_vec_v<8>(c->tune.hints, p, grid, block, st, pdl); break;
-#endif
+			case 1: e = launch_vec_v<1>(c->tune.hints & 1, p, grid, block, st, pdl); break;
+			case 2: e = launch_vec_v<2>(c->tune.hints & 1, p, grid, block, st, pdl); break;
+			case 4: e = launch_vec_v<4>(c->tune.hints & 1, p, grid, block, st, pdl); break;
 			default: return fail(LBM_ERR_ARG, "launch_step: vec %d", V);
 			}
 		}
@@ -652,15 +687,17 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 		const int tail = t0 + s != nsteps - 1;
 		if (!(flags && seam)) {
 			chain_open = false;
-			return launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[0], j0, j1, c->tune.hints && s == kk - 1);
+			return launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[0], j0, j1, tb_hint(c, s, kk));
 		}
 		if (!chain_open) {
 			if ((ce = cudaEventRecord(c->ev_main, c->stream[0])) != cudaSuccess) return (int)LBM_ERR_CUDA;
 			if ((ce = cudaStreamWaitEvent(c->stream[1], c->ev_main, 0)) != cudaSuccess) return (int)LBM_ERR_CUDA;
 			chain_open = true;
 		}
+		if (seam_fusable(c))                                         /* wait + step + announce in ONE launch */
+			return launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[1], j0, j1, tb_hint(c, s, kk), 1);
 		if ((r = launch_wait(c, c->stream[1]))) return r;
-		if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[1], j0, j1, c->tune.hints && s == kk - 1))) return r;
+		if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, c->stream[1], j0, j1, tb_hint(c, s, kk)))) return r;
 		return launch_signal(c, c->stream[1]);
 	});
 	if (ce != cudaSuccess) return fail(LBM_ERR_CUDA, "enqueue_macro: %s", cudaGetErrorString(ce));
@@ -1208,10 +1245,9 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	lbm_tuning n = *t;
 	if (n.vec == 0) n.vec = default_vec(c);
 	if (n.block == 0) n.block = 128;
-	const int vmax = 32 / (int)sizeof(real_t);
-	if ((n.vec != 1 && n.vec != 2 && n.vec != 4 && n.vec != 8) || n.vec > vmax) return fail(LBM_ERR_ARG, "lbm_set_tuning: vec %d", n.vec);
+	if (n.vec != 1 && n.vec != 2 && n.vec != 4) return fail(LBM_ERR_ARG, "lbm_set_tuning: vec %d", n.vec);
 	if (n.block < 32 || n.block > 512 || (n.block & 31)) return fail(LBM_ERR_ARG, "lbm_set_tuning: block %d", n.block);
-	if (n.hints < 0 || n.hints > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
+	if (n.hints < 0 || n.hints > 3 || (n.hints > 1 && !c->inplace)) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
@@ -1226,7 +1262,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 int lbm_set_experimental(lbm_ctx *c, const lbm_experimental *x)
 {
 	if (!c || !x) return fail(LBM_ERR_ARG, "lbm_set_experimental: null argument");
-	if (x->stage_smem < 0 || x->stage_smem > 2 || x->rows_per_thread < 0 || x->rows_per_thread > 1024) return fail(LBM_ERR_ARG, "lbm_set_experimental: stage_smem %d, rows_per_thread %d", x->stage_smem, x->rows_per_thread);
+	if (x->stage_smem < 0 || x->stage_smem > 2 || x->rows_per_thread < 0 || x->rows_per_thread > 1024 || x->smem_pad < 0 || x->smem_pad > 48 * 1024) return fail(LBM_ERR_ARG, "lbm_set_experimental: stage_smem %d, rows_per_thread %d", x->stage_smem, x->rows_per_thread);
 	drop_graph(c);
 	c->exp = *x;
 	return LBM_OK;
@@ -1387,7 +1423,7 @@ static int group_run_wavefront(lbm_ctx **slabs, int n, int nsteps)
 						tb_range(cols, cols.piece[ci], s, &j0, &j1);
 						if (r1 <= r0 || j1 <= j0) continue;
 						if (cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
-						if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1, c->tune.hints && s == kk - 1))) return rc;
+						if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[0], j0, j1, tb_hint(c, s, kk)))) return rc;
 					}
 				}
 				CK(cudaEventRecord(c->ev_main, c->stream[0]));
@@ -1407,7 +1443,7 @@ static int group_run_wavefront(lbm_ctx **slabs, int n, int nsteps)
 					if ((rc = set_device(c))) return rc;
 					CK(cudaStreamWaitEvent(c->stream[1], up->ev_bnd[prev], 0));
 					CK(cudaStreamWaitEvent(c->stream[1], dn->ev_bnd[prev], 0));
-					if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[1], j0, j1, c->tune.hints && s == kk - 1))) return rc;
+					if ((rc = launch_step(c, (t0 + s) & 1, r0, r1, t0 + s != nsteps - 1, c->stream[1], j0, j1, tb_hint(c, s, kk)))) return rc;
 				}
 				for (int p = 0; p < n; p++) {
 					lbm_ctx *c = slabs[p];

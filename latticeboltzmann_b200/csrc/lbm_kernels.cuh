@@ -62,6 +62,13 @@ template <typename T> struct StepParams {
 	int outflow;           // 0: y wraps periodically (WRAPAROUND 1, LB.c:42-43,233-234); 1: open ends, see pull_columns()
 	const uint32_t *slip;  // nullptr: every wall site bounces back (LB.c:246-255); else two bit planes [2][nxl][ldw]:
 	                       // plane 0 = "reflect" (slip, LB.c:21) walls whose normal is x, plane 1 = normal y
+	// Neighbour barrier folded into a seam launch of the in-place kernel (slabs of a ring living in other processes):
+	int *seam_flags;       // nullptr: none.  Else this slab's flag block: every CTA waits until [0] and [1] (the epochs the
+	                       // two neighbours have announced) reach seam_wait, or gives up (abort word [3], see flag_wait_kernel)
+	int *seam_up, *seam_dn;// the slots this slab announces in (neighbours' flag blocks): the LAST CTA to finish stores seam_signal
+	unsigned *seam_done;   // CTAs finished so far (zero between launches)
+	int seam_wait, seam_signal;
+	unsigned long long seam_timeout_ns;
 	T w0, w14, w58;        // OMEGA0/14/58 (LB.c:38-40), formed on the host in T
 	T itau;                // REAL_T(1.0)/TAU (LB.c:323)
 	double itau_d;         // (1.0/TAU) in double (LB.c:295,456)
@@ -443,65 +450,129 @@ stream_collide_vec_kernel(const __grid_constant__ StepParams<T> p)
 // memory, or this slab itself when P == 1); phase 2 pushes the three halo speeds like the A/B
 // kernel does.  Same bytes over NVLink per two steps as A/B.
 // ---------------------------------------------------------------------------
-// coherent loads (never ld.global.nc: the buffer is written by the same kernel)
-template <int V> __device__ __forceinline__ void ldc(const double *p, double (&v)[V])
+// L2 eviction priority of the in-place kernels' accesses (temporal blocking keeps a tile L2-resident for k levels):
+//   EP 0  default
+//   EP 1  evict_first: the stores of a tile's LAST level -- nothing reads them again before the tile has left L2
+//   EP 2  evict_last:  the loads and stores of the other levels -- the next level reads exactly these lines
+// (createpolicy + .L2::cache_hint accesses; always coherent loads, never ld.global.nc: the buffer is written by the same kernel)
+template <int EP> __device__ __forceinline__ uint64_t l2_policy()
 {
-	if constexpr (V == 1) v[0] = *p;
+	uint64_t pol = 0;
+	if constexpr (EP == 1) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+	if constexpr (EP == 2) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+	return pol;
+}
+template <int EP> __device__ __forceinline__ double ld_ep(const double *p, uint64_t pol)
+{
+	if constexpr (EP == 0) return *p;
+	double v;
+	asm volatile("ld.global.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+	return v;
+}
+template <int EP> __device__ __forceinline__ float ld_ep(const float *p, uint64_t pol)
+{
+	if constexpr (EP == 0) return *p;
+	float v;
+	asm volatile("ld.global.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
+	return v;
+}
+template <int EP> __device__ __forceinline__ void st_ep(double *p, double v, uint64_t pol)
+{
+	if constexpr (EP == 0) *p = v;
+	else asm volatile("st.global.L2::cache_hint.f64 [%0], %1, %2;" ::"l"(p), "d"(v), "l"(pol));
+}
+template <int EP> __device__ __forceinline__ void st_ep(float *p, float v, uint64_t pol)
+{
+	if constexpr (EP == 0) *p = v;
+	else asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(p), "f"(v), "l"(pol));
+}
+template <int V, int EP> __device__ __forceinline__ void ldc(const double *p, double (&v)[V], uint64_t pol)
+{
+	if constexpr (V == 1) v[0] = ld_ep<EP>(p, pol);
 	else {
 #pragma unroll
-		for (int k = 0; k < V; k += 2) { const double2 t = *reinterpret_cast<const double2 *>(p + k); v[k] = t.x; v[k + 1] = t.y; }
+		for (int k = 0; k < V; k += 2) {
+			if constexpr (EP == 0) { const double2 t = *reinterpret_cast<const double2 *>(p + k); v[k] = t.x; v[k + 1] = t.y; }
+			else asm volatile("ld.global.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;" : "=d"(v[k]), "=d"(v[k + 1]) : "l"(p + k), "l"(pol));
+		}
 	}
 }
-template <int V> __device__ __forceinline__ void ldc(const float *p, float (&v)[V])
+template <int V, int EP> __device__ __forceinline__ void ldc(const float *p, float (&v)[V], uint64_t pol)
 {
-	if constexpr (V == 1) v[0] = *p;
-	else if constexpr (V == 2) { const float2 t = *reinterpret_cast<const float2 *>(p); v[0] = t.x; v[1] = t.y; }
+	if constexpr (V == 1) v[0] = ld_ep<EP>(p, pol);
+	else if constexpr (V == 2) {
+		if constexpr (EP == 0) { const float2 t = *reinterpret_cast<const float2 *>(p); v[0] = t.x; v[1] = t.y; }
+		else asm volatile("ld.global.L2::cache_hint.v2.f32 {%0,%1}, [%2], %3;" : "=f"(v[0]), "=f"(v[1]) : "l"(p), "l"(pol));
+	} else {
+#pragma unroll
+		for (int k = 0; k < V; k += 4) {
+			if constexpr (EP == 0) { const float4 t = *reinterpret_cast<const float4 *>(p + k); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
+			else asm volatile("ld.global.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;" : "=f"(v[k]), "=f"(v[k + 1]), "=f"(v[k + 2]), "=f"(v[k + 3]) : "l"(p + k), "l"(pol));
+		}
+	}
+}
+template <int V, int EP> __device__ __forceinline__ void ste(double *p, const double (&v)[V], uint64_t pol)
+{
+	if constexpr (EP == 0) stv<0, V>(p, v);
+	else if constexpr (V == 1) st_ep<EP>(p, v[0], pol);
 	else {
 #pragma unroll
-		for (int k = 0; k < V; k += 4) { const float4 t = *reinterpret_cast<const float4 *>(p + k); v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w; }
+		for (int k = 0; k < V; k += 2)
+			asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1,%2}, %3;" ::"l"(p + k), "d"(v[k]), "d"(v[k + 1]), "l"(pol));
+	}
+}
+template <int V, int EP> __device__ __forceinline__ void ste(float *p, const float (&v)[V], uint64_t pol)
+{
+	if constexpr (EP == 0) stv<0, V>(p, v);
+	else if constexpr (V == 1) st_ep<EP>(p, v[0], pol);
+	else if constexpr (V == 2) asm volatile("st.global.L2::cache_hint.v2.f32 [%0], {%1,%2}, %3;" ::"l"(p), "f"(v[0]), "f"(v[1]), "l"(pol));
+	else {
+#pragma unroll
+		for (int k = 0; k < V; k += 4)
+			asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p + k), "f"(v[k]), "f"(v[k + 1]), "f"(v[k + 2]), "f"(v[k + 3]), "l"(pol));
 	}
 }
 // V values to columns (j0-1 .. j0+V-2) [DJ < 0, the first one goes to jl] or (j0+1 .. j0+V) [DJ > 0, the last one goes to jr].
 // Periodic ends: jl / jr are the wrapped columns.  Open ends (outflow): what would leave the lattice is dropped and the
 // end column's site stores a second copy of the value that stays at the end (the zero-gradient end of pull_columns()):
 // the slot the wrap would have filled.
-template <typename T, int V, int DJ> __device__ __forceinline__ void st_shifted(T *row, int j0, int jl, int jr, int ny, int outflow, const T (&v)[V])
+template <typename T, int V, int DJ, int EP> __device__ __forceinline__ void st_shifted(T *row, int j0, int jl, int jr, int ny, int outflow, const T (&v)[V], uint64_t pol)
 {
 	if constexpr (DJ < 0) {
-		if (!(outflow && j0 == 0)) row[jl] = v[0];
-		if (outflow && j0 + V == ny) row[ny - 1] = v[V - 1];
-		if constexpr (V == 2) row[j0] = v[1];
+		if (!(outflow && j0 == 0)) st_ep<EP>(row + jl, v[0], pol);
+		if (outflow && j0 + V == ny) st_ep<EP>(row + ny - 1, v[V - 1], pol);
+		if constexpr (V == 2) st_ep<EP>(row + j0, v[1], pol);
 		if constexpr (V >= 4) {
 #pragma unroll
 			for (int k = 1; k + 1 < V; k += 2) {            // pairs (1,2),(3,4),... start at the even column j0+k-1
 				T pr[2] = {v[k], v[k + 1]};
-				stv<0, 2>(row + j0 + k - 1, pr);
+				ste<2, EP>(row + j0 + k - 1, pr, pol);
 			}
-			row[j0 + V - 2] = v[V - 1];
+			st_ep<EP>(row + j0 + V - 2, v[V - 1], pol);
 		}
 	} else {
-		if (!(outflow && j0 + V == ny)) row[jr] = v[V - 1];
-		if (outflow && j0 == 0) row[0] = v[0];
-		if constexpr (V == 2) row[j0 + 1] = v[0];
+		if (!(outflow && j0 + V == ny)) st_ep<EP>(row + jr, v[V - 1], pol);
+		if (outflow && j0 == 0) st_ep<EP>(row, v[0], pol);
+		if constexpr (V == 2) st_ep<EP>(row + j0 + 1, v[0], pol);
 		if constexpr (V >= 4) {
-			row[j0 + 1] = v[0];
+			st_ep<EP>(row + j0 + 1, v[0], pol);
 #pragma unroll
 			for (int k = 1; k + 1 < V; k += 2) {            // pairs (1,2),(3,4),... land on the even column j0+k+1
 				T pr[2] = {v[k], v[k + 1]};
-				stv<0, 2>(row + j0 + k + 1, pr);
+				ste<2, EP>(row + j0 + k + 1, pr, pol);
 			}
 		}
 	}
 }
 
 // the nine populations the V sites (r, j0..j0+V-1) relax this step
-template <typename T, int V, int PHASE>
-__device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T (&f)[9][V])
+template <typename T, int V, int PHASE, int EP = 0>
+__device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T (&f)[9][V], unsigned lanes, uint64_t pol = 0)
 {
 	const T *const own = p.dst + (size_t)(r + 1) * p.ldy;    // p.src == p.dst
 	if constexpr (PHASE == 2) {
 #pragma unroll
-		for (int s = 0; s < 9; s++) ldc<V>(own + (size_t)opposite(s) * p.plane + j0, f[s]);
+		for (int s = 0; s < 9; s++) ldc<V, EP>(own + (size_t)opposite(s) * p.plane + j0, f[s], pol);
 	} else {
 		int jl, jr;
 		pull_columns(p, j0, V, jl, jr);
@@ -510,19 +581,19 @@ __device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T
 		for (int s = 0; s < 9; s++) {
 			const T *b = lrow[pull_di(s) + 1] + (size_t)s * p.plane;
 			if constexpr (V == 1) {
-				f[s][0] = b[pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0];
+				f[s][0] = ld_ep<EP>(b + (pull_dj(s) < 0 ? jl : pull_dj(s) > 0 ? jr : j0), pol);
 			} else {
 				T al[V];
-				ldc<V>(b + j0, al);
+				ldc<V, EP>(b + j0, al, pol);
 				if (pull_dj(s) == 0) {
 #pragma unroll
 					for (int k = 0; k < V; k++) f[s][k] = al[k];
 				} else if (pull_dj(s) < 0) {
-					f[s][0] = b[jl];
+					f[s][0] = ld_ep<EP>(b + jl, pol);
 #pragma unroll
 					for (int k = 1; k < V; k++) f[s][k] = al[k - 1];
 				} else {
-					f[s][V - 1] = b[jr];
+					f[s][V - 1] = ld_ep<EP>(b + jr, pol);
 #pragma unroll
 					for (int k = 0; k < V - 1; k++) f[s][k] = al[k + 1];
 				}
@@ -530,20 +601,18 @@ __device__ __forceinline__ void aa_load(const StepParams<T> &p, int r, int j0, T
 		}
 		// Open ends only: the end column's site reads a slot its in-row neighbour also reads and then overwrites (the one
 		// slot with two readers).  Both are lanes of one warp (V == 1: adjacent lanes, column ranges start at multiples
-		// of 8; V > 1: one thread); order every lane's loads before any lane's stores.
-		if (p.outflow) __syncwarp();
+		// of 8; V > 1: one thread); order every lane's loads before any lane's stores (`lanes`: the warp's lanes that work).
+		if (p.outflow) __syncwarp(lanes);
 	}
 }
 
-// HINT 1: streaming (evict-first) stores -- the last level of a temporal-blocking macro-step, whose results are not read
-// again before the tile has left L2 anyway
-template <typename T, int V, int PHASE, int HINT>
-__device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, const T (&o)[9][V])
+template <typename T, int V, int PHASE, int EP>
+__device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, const T (&o)[9][V], uint64_t pol = 0)
 {
 	T *const own = p.dst + (size_t)(r + 1) * p.ldy;
 	if constexpr (PHASE == 2) {
 #pragma unroll
-		for (int s = 0; s < 9; s++) stv<HINT, V>(own + (size_t)s * p.plane + j0, o[s]);
+		for (int s = 0; s < 9; s++) ste<V, EP>(own + (size_t)s * p.plane + j0, o[s], pol);
 		if (r == 0) {                                        // as in the A/B kernel (LB.c:239,242,243)
 			stv<0, V>(p.dn_halo + 4 * p.dn_plane + j0, o[4]);
 			stv<0, V>(p.dn_halo + 7 * p.dn_plane + j0, o[7]);
@@ -566,9 +635,9 @@ __device__ __forceinline__ void aa_store(const StepParams<T> &p, int r, int j0, 
 #pragma unroll
 		for (int k = 0; k < 9; k++) {
 			T *b = srow[pull_di(k) + 1] + (size_t)k * spl[pull_di(k) + 1];
-			if (pull_dj(k) == 0) stv<HINT, V>(b + j0, o[opposite(k)]);
-			else if (pull_dj(k) < 0) st_shifted<T, V, -1>(b, j0, jl, jr, p.ny, p.outflow, o[opposite(k)]);
-			else st_shifted<T, V, 1>(b, j0, jl, jr, p.ny, p.outflow, o[opposite(k)]);
+			if (pull_dj(k) == 0) ste<V, EP>(b + j0, o[opposite(k)], pol);
+			else if (pull_dj(k) < 0) st_shifted<T, V, -1, EP>(b, j0, jl, jr, p.ny, p.outflow, o[opposite(k)], pol);
+			else st_shifted<T, V, 1, EP>(b, j0, jl, jr, p.ny, p.outflow, o[opposite(k)], pol);
 		}
 	}
 }
@@ -590,7 +659,32 @@ template <typename T> __device__ __forceinline__ int aa_row(const StepParams<T> 
 #else
 #define LBM_AA_BOUNDS __launch_bounds__(sizeof(T) == 4 ? 256 : 512, sizeof(T) == 4 ? 4 : 0)
 #endif
-template <typename T, int V, int PHASE, int HINT>
+// ---- neighbour barrier between ranks living in different processes / GPUs ----
+// The spinners live on DIFFERENT GPUs than the signallers.  flags[3] is the ring's abort word: a wait that gives up after
+// ~timeout_ns raises it here AND in both neighbours' flag blocks, every wait returns at once when it finds it raised, so
+// one stalled rank stops the whole ring within one time-out instead of one per remaining wait; lbm_sync reports it.
+// Returns false if the ring is aborting (the caller then skips its work: the halos it would read are stale).
+__device__ __forceinline__ bool seam_wait_flags(volatile int *flags, volatile int *up_abort, volatile int *dn_abort, int epoch, unsigned long long timeout_ns)
+{
+	if (flags[3]) return false;
+	if (flags[0] >= epoch && flags[1] >= epoch) { __threadfence_system(); return true; }
+	unsigned long long t0;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+	while (flags[0] < epoch || flags[1] < epoch) {
+		unsigned long long t;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+		if (flags[3] || t - t0 > timeout_ns) {
+			flags[3] = 1; *up_abort = 1; *dn_abort = 1;
+			__threadfence_system();
+			return false;
+		}
+		__nanosleep(100);
+	}
+	__threadfence_system();
+	return true;
+}
+
+template <typename T, int V, int PHASE, int HINT, bool SEAM = false>
 __global__ void LBM_AA_BOUNDS
 stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 {
@@ -601,13 +695,37 @@ stream_collide_aa_kernel(const __grid_constant__ StepParams<T> p)
 	int j0 = p.jmin + (int)jv * V;
 	if (j0 >= p.ny) j0 -= p.ny;                              // column ranges of the 2-D wavefront schedule may wrap (jmax > ny)
 	asm volatile("griddepcontrol.wait;" ::: "memory");
-	if (jv >= nvec) return;                                  // (exited lanes do not take part in aa_load's __syncwarp())
-	for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
-		const int r = aa_row(p, rr);
-		T f[9][V], o[9][V];
-		aa_load<T, V, PHASE>(p, r, j0, f);
-		relax_sites<T, V>(p, f, o, r, j0, p.tail_source);
-		aa_store<T, V, PHASE, HINT>(p, r, j0, o);
+	bool live = jv < nvec;
+	unsigned lanes = 0xffffffffu;                            // the lanes of this warp that work (exited ones need not be named)
+	if constexpr (SEAM) {                                    // seam launch of a slab: both neighbours must have announced seam_wait
+		__shared__ int go;
+		if (threadIdx.x == 0) go = seam_wait_flags(p.seam_flags, p.seam_up + 3, p.seam_dn + 2, p.seam_wait, p.seam_timeout_ns);
+		__syncthreads();
+		live = live && go;
+		lanes = __ballot_sync(0xffffffffu, live);            // idle lanes stay for the closing __syncthreads()
+	} else if (!live) return;
+	const uint64_t pol = l2_policy<HINT>();                  // HINT 1: evict-first stores; HINT 2: evict-last loads and stores
+	if (live)
+		for (uint32_t rr = blockIdx.y; rr < rows; rr += gridDim.y) {
+			const int r = aa_row(p, rr);
+			T f[9][V], o[9][V];
+			aa_load<T, V, PHASE, HINT == 2 ? 2 : 0>(p, r, j0, f, lanes, pol);
+			relax_sites<T, V>(p, f, o, r, j0, p.tail_source);
+			aa_store<T, V, PHASE, HINT>(p, r, j0, o, pol);
+		}
+	if constexpr (SEAM) {                                    // announce: the last CTA to finish publishes this slab's epoch
+		__syncthreads();                                         // every store of this CTA is issued ...
+		if (threadIdx.x == 0) {
+			__threadfence_system();                              // ... and performed (peer stores included) before the count moves
+			const unsigned n = gridDim.x * gridDim.y;
+			if (atomicAdd(p.seam_done, 1u) == n - 1u) {
+				*p.seam_done = 0u;
+				__threadfence_system();
+				*(volatile int *)p.seam_up = p.seam_signal;
+				*(volatile int *)p.seam_dn = p.seam_signal;
+				__threadfence_system();
+			}
+		}
 	}
 }
 
@@ -940,26 +1058,10 @@ __global__ void flag_signal_kernel(volatile int *up_slot, volatile int *dn_slot,
 	*dn_slot = epoch;
 	__threadfence_system();
 }
-// wait: spin until both neighbours have announced `epoch`.  The spinners live on DIFFERENT
-// GPUs than the signallers.  flags[3] is the ring's abort word: a wait that gives up after
-// ~timeout_ns raises it here AND in both neighbours' flag blocks, every wait returns at once
-// when it finds it raised (at entry or while spinning), so one stalled rank stops the whole
-// ring within one time-out instead of one time-out per remaining wait; lbm_sync reports it.
-__global__ void flag_wait_kernel(volatile int *flags, volatile int *up_abort, volatile int *dn_abort, int epoch, unsigned long long timeout_ns)
+// wait (the unfused form, for the launches that cannot carry the barrier themselves): see seam_wait_flags
+__global__ void flag_wait_kernel(int *flags, int *up_abort, int *dn_abort, int epoch, unsigned long long timeout_ns)
 {
-	if (flags[3]) return;
-	unsigned long long t0;
-	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-	while (flags[0] < epoch || flags[1] < epoch) {
-		unsigned long long t;
-		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-		if (flags[3] || t - t0 > timeout_ns) {
-			flags[3] = 1; *up_abort = 1; *dn_abort = 1;
-			break;
-		}
-		__nanosleep(200);
-	}
-	__threadfence_system();
+	seam_wait_flags(flags, up_abort, dn_abort, epoch, timeout_ns);
 }
 
 } // namespace lbm

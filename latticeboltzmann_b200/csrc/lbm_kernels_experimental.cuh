@@ -72,7 +72,7 @@ stream_collide_aa_staged_kernel(const __grid_constant__ StepParams<T> p)
 #pragma unroll
 		for (int s = 0; s < 9; s++) f[s][0] = mine[(b * 9u + (uint32_t)s) * bd];
 		relax_sites<T, 1>(p, f, o, r, j0, p.tail_source);
-		aa_store<T, 1, PHASE, 0>(p, r, j0, o);
+		aa_store<T, 1, PHASE, 0>(p, r, j0, o, 0);
 		b ^= 1u;
 	}
 }

@@ -36,14 +36,14 @@ def ring_inputs(prec, nx, ny):
     return fA, walls
 
 
-def ring_parity(local_device, log=None):
-    """Runs every case of ``ring_cases`` over the ranks of the default process group; returns (passed, total) on every rank."""
-    import torch
+def ring_parity(local_device, log=None, staged=True):
+    """Runs every case of ``ring_cases`` over the ranks of the default process group; returns (passed, total) on every rank.
+    ``staged=False`` leaves out the NCCL-staged transport (ranks sharing one GPU talk over gloo)."""
     import torch.distributed as dist
     from .slab import DistributedLattice
     from .solver import Lattice
     rank, world = dist.get_rank(), dist.get_world_size()
-    cases = ring_cases(world)
+    cases = [c for c in ring_cases(world) if staged or c[1] != "staged"]
     nsame = 0
     for prec, transport, nx, ny, engine in cases:
         fA, walls = ring_inputs(prec, nx, ny)
@@ -83,6 +83,41 @@ def ring_parity(local_device, log=None):
                     log("   first differing elements (s,i,j): " + str(np.argwhere(got != want)[:5].tolist()))
         dl.close()
         dist.barrier()
-    n = torch.tensor([nsame], device="cuda")
-    dist.broadcast(n, 0)
-    return int(n.item()), len(cases)
+    box = [nsame]
+    dist.broadcast_object_list(box, 0)                       # (works under NCCL and under gloo)
+    return int(box[0]), len(cases)
+
+
+def abort_check(local_device, timeout_ms=400):
+    """One rank of a 2-rank ring stops stepping: the other rank's waits must give up after ONE time-out (the ring's abort word),
+    lbm_sync must report it, and nothing may hang.  Returns (seconds rank 0 spent, error text) on rank 0."""
+    import os
+    import torch.distributed as dist
+    from ._capi import LbmError
+    from .slab import DistributedLattice
+    rank = dist.get_rank()
+    os.environ["LBM_WAIT_TIMEOUT_MS"] = str(timeout_ms)
+    try:
+        nx, ny = 64, 264
+        fA, walls = ring_inputs("dp", nx, ny)
+        dl = DistributedLattice(nx, ny, "dp", "p2p", device=local_device, inplace=True)
+        dl.lat.set_tuning(tb_depth=4, tb_rows=4, tb_cols=64)          # dozens of seam waits per run
+        dl.lat.upload(fA, walls)
+        dist.barrier()
+        dl.run(8)
+        dl.lat.sync()
+        dist.barrier()
+        out = None
+        if rank == 0:                                            # rank 1 does not step any more
+            t0 = time.time()
+            try:
+                dl.run(40)
+                dl.lat.sync()
+                out = (time.time() - t0, "no error")
+            except LbmError as exc:
+                out = (time.time() - t0, str(exc))
+        dist.barrier()
+        dl.close()
+        return out
+    finally:
+        os.environ.pop("LBM_WAIT_TIMEOUT_MS", None)

@@ -123,7 +123,7 @@ def test_cuda_matches_oracle_shapes(prec, isa, shape):
 
 
 def _variants(prec):
-    vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
+    vecs = (1, 2, 4)
     out = []
     for v in vecs:
         for hints in (0, 1):
@@ -147,7 +147,7 @@ def test_every_kernel_variant_is_bit_identical(prec):
             _assert_same(lat.download("A"), o.f_view("A"), f"fA with {tune}")
             _assert_same(lat.download("B"), o.f_view("B"), f"fB with {tune}")
     # the in-place kernels: every vector width, a few CTA shapes, PDL/graph
-    vecs = (1, 2, 4) if prec == "dp" else (1, 2, 4, 8)
+    vecs = (1, 2, 4)
     with _lattice(c, inplace=True) as lat:
         for v in vecs:
             for extra in (dict(block=128), dict(block=256), dict(block=64, pdl=1, graph=2), dict(block=512, pdl=1), dict(block=96),

@@ -1,5 +1,5 @@
 """Short, deterministic workload for ncu: a few steps of the step kernel on the BASELINE lattices.
-usage: profile_target.py [dp|sp] [small|large|c3] [nsteps] [ab|inplace|staged:<mode>:<rows_per_thread>]
+usage: profile_target.py [dp|sp] [small|large|c3] [nsteps] [ab|inplace|inplace:<hints>|staged:<mode>:<rows_per_thread>]
 (inplace = one buffer, AA kernels, library-default temporal blocking -- what bench.py's headline runs)"""
 import os
 import sys
@@ -15,8 +15,10 @@ engine = sys.argv[4] if len(sys.argv) > 4 else "ab"
 nx, ny = {"small": (400, 4000), "large": (8192, 32768), "c3": (800, 4000)}[size]
 with Lattice(nx, ny, prec, inplace=(engine != "ab"), experimental=engine.startswith("staged")) as lat:
     lat.InitializeArrays()
-    if engine == "inplace":
+    if engine.startswith("inplace"):
         lat.set_tuning(graph=0)          # individual launches, so that ncu sees every kernel
+        if ":" in engine:                # L2 eviction-priority hints of the temporal-blocking levels (lbm_tuning.hints)
+            lat.set_tuning(graph=0, hints=int(engine.split(":")[1]))
     if engine.startswith("staged"):      # experiment build: next row staged in shared memory (cp.async / TMA), no temporal blocking
         _, mode, rpt = engine.split(":")
         lat.set_tuning(graph=0, pdl=1, tb_depth=0, vec=1)
