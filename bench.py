@@ -77,7 +77,8 @@ def measured_peak():
 def l2_roof():
     d = read_json("profiles", "l2_peak.json")
     if d and d.get("l2_gbs"):
-        return float(d["l2_gbs"]), "measured L2-resident in-place update (profiles/l2_peak.json, tools/l2_peak_probe.py)"
+        return float(d["l2_gbs"]), ("measured: L2-resident in-place update, persistent sweeps with nothing ordering them "
+                                    "(profiles/l2_peak.json, tools/l2_peak_probe.py; one launch per sweep reaches %s GB/s)" % d.get("l2_launch_per_sweep_gbs"))
     return None, "unmeasured (profiles/l2_peak.json absent)"
 
 
