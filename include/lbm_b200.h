@@ -219,9 +219,10 @@ int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary strea
 typedef struct {
 	int vec;          /* sites per thread: 1, 2 or 4; 0 = by lattice size (DP: 1 up to 16 Mi sites and in place, else 4; SP: 4) */
 	int block;        /* threads per CTA; 0 = default 128 (the SP in-place kernels run at most 256) */
-	int hints;        /* 1: A/B kernel: L1::no_allocate loads + streaming stores; in-place kernels under temporal blocking: the LAST
-	                     level of a macro-step stores with the evict-first policy (its results are not read again while the tile
-	                     is L2-resident).  0 = default caching */
+	int hints;        /* bit 0: A/B kernel: L1::no_allocate loads + streaming stores; in-place kernels under temporal blocking: the
+	                     LAST level of a macro-step stores with the L2 evict-first policy (its results are not read again
+	                     while the tile is L2-resident).  bit 1 (in-place contexts): the other levels load and store with the
+	                     evict-last policy.  0 = default caching; measured neutral, never changes results */
 	int pdl;          /* 1: step kernels are launched with programmatic dependent launch, so the next
 	                     step's CTAs are resident (waiting in griddepcontrol.wait) while this one drains */
 	int graph;        /* >0: steps are replayed from a captured CUDA graph of `graph` step pairs (single-slab contexts) */
