@@ -236,6 +236,9 @@ typedef struct {
 	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
 	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 16 KB
 	                     row segments, 32 KB on slabs, only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
+	int tb_chains;    /* concurrent tile chains of the temporal-blocking schedule (1..4; 0 = 1): the slab's rows are cut into this many
+	                     lanes that run their tiles on separate streams, each with its share of the L2 tile budget, the boundaries
+	                     between lanes handled like slab seams.  A second chain fills the drain every tile level pays. */
 } lbm_tuning;
 int lbm_set_tuning(lbm_ctx *ctx, const lbm_tuning *t);
 int lbm_get_tuning(lbm_ctx *ctx, lbm_tuning *t);
@@ -249,6 +252,13 @@ long long lbm_kernel_launches(lbm_ctx *ctx);
  * ring, 0 = lattice too small, plain stepping).  Returns the number of launches (which may exceed cap; only cap
  * entries are written), -1 on bad arguments. */
 int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
+/* The same for lbm_tuning.tb_chains > 1 (concurrent tile chains): 7 ints per launch, (level, r0, r1, j0, j1, stream, outer), in
+ * enqueue order, which is also a valid sequential order.  stream 0..C-1 = the lanes' own tiles, C..2C-1 = the seam chain of the
+ * boundary after lane (stream - C), whose launches of one column piece start after lanes b and b+1 have finished their tiles of
+ * that piece; outer = 1 marks the boundary between the last lane and the first (the periodic wrap / the slab seam).
+ * *chains_used < 2: the slab is too low for lanes, lbm_tb_schedule describes what runs.  Host logic only. */
+int lbm_tb_schedule_chains(int nx, int ny, int multi, int chains, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *chains_used,
+                           int *launches, int cap);
 
 #ifdef __cplusplus
 }

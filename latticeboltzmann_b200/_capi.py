@@ -44,7 +44,8 @@ def _structs(real):
 
     class Tuning(ctypes.Structure):
         _fields_ = [("vec", ctypes.c_int), ("block", ctypes.c_int), ("hints", ctypes.c_int), ("pdl", ctypes.c_int),
-                    ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int), ("tb_cols", ctypes.c_int)]
+                    ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int), ("tb_cols", ctypes.c_int),
+                    ("tb_chains", ctypes.c_int)]
 
     class Experimental(ctypes.Structure):      # include/lbm_b200_experimental.h (experiment build only)
         _fields_ = [("stage_smem", ctypes.c_int), ("rows_per_thread", ctypes.c_int), ("smem_pad", ctypes.c_int)]
@@ -60,7 +61,7 @@ SYMBOLS = [
     "lbm_compute_reynolds", "lbm_reynolds_column", "lbm_reynolds_from_column", "lbm_macroscopic",
     "lbm_print_lattice", "lbm_print_lattice_group", "lbm_checksum", "lbm_check_finite", "lbm_slab_info_get", "lbm_ipc_export", "lbm_ipc_connect", "lbm_connect_local",
     "lbm_group_run", "lbm_halo_pack", "lbm_halo_unpack", "lbm_step_rows", "lbm_stream_handle",
-    "lbm_stream_join", "lbm_set_tuning", "lbm_get_tuning", "lbm_kernel_launches", "lbm_tb_schedule",
+    "lbm_stream_join", "lbm_set_tuning", "lbm_get_tuning", "lbm_kernel_launches", "lbm_tb_schedule", "lbm_tb_schedule_chains",
 ]
 
 
@@ -93,6 +94,8 @@ class Lib:
         d.lbm_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(self.Config)]
         d.lbm_tb_schedule.restype = ci
         d.lbm_tb_schedule.argtypes = [ci, ci, ci, ci, ci, ci, ctypes.POINTER(ci), vp, ci]
+        d.lbm_tb_schedule_chains.restype = ci
+        d.lbm_tb_schedule_chains.argtypes = [ci, ci, ci, ci, ci, ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ci), vp, ci]
         for name, args in {
             "lbm_destroy": [vp], "lbm_initialize_arrays": [vp, ctypes.POINTER(self.Scene)],
             "lbm_upload": [vp, vp, vp, vp, ci], "lbm_download": [vp, vp, vp, vp, ci],

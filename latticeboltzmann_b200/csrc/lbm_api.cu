@@ -66,6 +66,8 @@ static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "blob too large");
 
 } // namespace
 
+enum { LBM_MAX_CHAINS = 4 };
+
 struct lbm_ctx {
 	lbm_config cfg;
 	int nxl, ny, vw, nyvec, ldy, ldw;
@@ -96,6 +98,11 @@ struct lbm_ctx {
 	cudaGraphExec_t wf_exec;     // captured wavefront macro-step (wf_k timesteps, bands of wf_h rows)
 	long long wf_launches;       // kernels in that graph
 	int in_wavefront;            // set while run_wavefront enqueues (step kernels may then use PDL on slabs too)
+	/* concurrent tile chains (lbm_tuning.tb_chains): lane l > 0 runs on lane_stream[l] (lane 0 on stream[0]); the seam chain of
+	 * the boundary between lanes b and b+1 on chain_stream[b] (the outer boundary -- the periodic wrap / the slab seam -- on stream[1]) */
+	cudaStream_t lane_stream[LBM_MAX_CHAINS], chain_stream[LBM_MAX_CHAINS];
+	cudaEvent_t ev_lane[LBM_MAX_CHAINS], ev_chain[LBM_MAX_CHAINS], ev_fork;
+	int lanes_ready;
 #ifdef LBM_EXPERIMENTAL
 	lbm_experimental exp;
 #endif
@@ -272,6 +279,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	 * 43.7 vs 41.1 GLUPS at 400x4000 (profiles/r01_run3); no gain for SP or for large lattices */
 	c->tune.pdl = default_small_dp(c);
 	c->tune.graph = default_small_dp(c) ? 10 : 0;
+	c->tune.tb_chains = 1;
 	if (c->inplace && (unsigned long long)c->nxl * c->ny > (16ull << 20)) {
 		/* wide / large in-place lattices (profiles/r01_run14): 2-D tiles of ~60 MB, plain PDL launches (replaying
 		 * thousands of kernel nodes from a graph measured 5-10 % slower).  DP 8192x32768: 62.1 vs 47.8 GLUPS. */
@@ -279,6 +287,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		c->tune.graph = 0;
 		c->tune.tb_depth = 16;                                   /* SP since its kernels run at 64 registers: 104.4 (k 16) vs 102.1 (k 8), r01_run28 */
 		c->tune.vec = sizeof(real_t) == 8 ? 1 : 4;
+		c->tune.tb_chains = 2;                                   /* two concurrent tile chains: DP 57.4 -> 65.6 GLUPS, SP 102.2 -> 119.5 (profiles/r02_run6) */
 	}
 	if (c->inplace && (unsigned long long)c->nxl * c->ny <= (16ull << 20)) {
 		/* in-place small lattices (profiles/r01_run8, r01_run9): PDL + graph replay for both precisions; lattices
@@ -313,6 +322,13 @@ int lbm_destroy(lbm_ctx *c)
 	if (c->flags) cudaFree(c->flags);
 	if (c->slip) cudaFree(c->slip);
 	if (c->seam_done) cudaFree(c->seam_done);
+	for (int k = 0; k < LBM_MAX_CHAINS; k++) {
+		if (c->lane_stream[k]) cudaStreamDestroy(c->lane_stream[k]);
+		if (c->chain_stream[k]) cudaStreamDestroy(c->chain_stream[k]);
+		if (c->ev_lane[k]) cudaEventDestroy(c->ev_lane[k]);
+		if (c->ev_chain[k]) cudaEventDestroy(c->ev_chain[k]);
+	}
+	if (c->ev_fork) cudaEventDestroy(c->ev_fork);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
 	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
 	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -612,11 +628,12 @@ void tb_axis(TbAxis *ax, int n, int g, int e, int k, int P)
 /* multi != 0: this slab is one of several.  Every slab of a ring must then walk the SAME sequence of (column piece,
  * level) events, so the depth is never clamped to the slab: a slab too low for the row pyramid (2k + 2 > nx)
  * takes whole-slab launches per event instead of row pieces. */
-void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols)
+void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols, int chains = 1)
 {
+	const int edge = multi != 0 || chains > 1;                  /* first and last row belong to the seam piece (a slab of a ring, a lane) */
 	const int G = 8;                                             /* column skew per level: keeps every vector width aligned */
 	int k = tb_depth & ~1;
-	if (!multi)
+	if (!edge)
 		while (k >= 2 && 2 * k + 2 > nx) k -= 2;                 /* pyramid base >= 2k inside the ring */
 	pl->k = k < 2 ? 0 : k;
 	if (!pl->k) return;
@@ -638,14 +655,17 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int 
 		W += G * k;
 		budget = 60e6;
 	}
-	if (2 * k + 2 + 2 * (multi != 0) > nx) {                     /* (multi only) no room for the row pyramid */
+	/* several concurrent chains share the L2: measured best per chain at 8192x32768 (profiles/r02_run6 two_chain_*.log):
+	 * 24 MB (DP) / 36 MB (SP) with two chains */
+	if (chains > 1) budget = (sizeof(real_t) == 8 ? 48e6 : 72e6) / chains;
+	if (2 * k + 2 + 2 * edge > nx) {                             /* (slabs, lanes) no room for the row pyramid */
 		pl->rows.n = nx; pl->rows.g = 1; pl->rows.e = 0; pl->rows.npieces = 1;
 		pl->rows.piece[0] = TbPiece{TB_WHOLE, 0, nx};
 		return;
 	}
 	int H = tb_rows;
 	if (H <= 0) H = (int)(budget / (cell * W)) - k;
-	tb_axis(&pl->rows, nx, 1, multi != 0, k, H < 2 ? 2 : H);
+	tb_axis(&pl->rows, nx, 1, edge, k, H < 2 ? 2 : H);
 }
 
 /* the launches of one macro-step of kk <= pl.k levels, in order: visit(level, r0, r1, j0, j1); r1 / j1 may exceed
@@ -709,18 +729,160 @@ int enqueue_macro(lbm_ctx *c, int t0, int kk, const TbPlan &pl, int nsteps)
 	return LBM_OK;
 }
 
+/* ---- concurrent tile chains ("lanes") ----
+ * Every level of a tile is one launch, and a launch loses about one CTA lifetime (~2 us) at its drain: the next level's CTAs are
+ * resident (PDL) but must wait until the last CTA of this level is done.  A second, independent chain of launches fills that
+ * gap (tools/two_chain_probe.py: DP 8192x32768 57.4 -> 65.6 GLUPS, SP 102.2 -> 119.5).  The rows of the slab are
+ * cut into C lanes; each lane walks the schedule of a slab of a ring on its own stream (row axis with e = 1: pyramid from its
+ * second row, parallelograms up to its last but one), and the boundary between lanes b and b+1 gets what a slab seam gets: an
+ * inverted pyramid (rows [B-1-s, B+1+s) at level s) whose chain of launches runs on a stream of its own after both lanes'
+ * tiles of the same column piece, beside their tiles of the next one.  Same buffer, same kernels, no halo in between: the
+ * dependency argument is the one of the slab schedule (a lane's tiles never need seam rows of the same macro-step; a seam
+ * launch needs the two lanes' tiles of its column piece and its own previous level).  The boundary between the last lane and
+ * the first is the periodic wrap of a single slab or the seam of a ring (then it carries the neighbour barrier as before). */
+struct LanePlan { int k, C; int base[LBM_MAX_CHAINS + 1]; TbAxis rows[LBM_MAX_CHAINS]; TbAxis cols; };
+
+/* returns the number of lanes used (< 2: take the single-chain schedule) */
+int tb_plan_lanes(LanePlan *lp, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols, int chains)
+{
+	static thread_local TbPlan pl;
+	int k = tb_depth & ~1;
+	if (k < 2 || chains < 2) return 1;
+	int C = chains > LBM_MAX_CHAINS ? LBM_MAX_CHAINS : chains;
+	if (C > nx / (2 * k + 4)) C = nx / (2 * k + 4);              /* every lane needs room for its row pyramid */
+	if (C < 2) return 1;
+	lp->k = k; lp->C = C;
+	for (int l = 0; l <= C; l++) lp->base[l] = (int)((long long)nx * l / C);
+	for (int l = 0; l < C; l++) {
+		tb_plan(&pl, lp->base[l + 1] - lp->base[l], ny, ldy, strips_ok, multi, k, tb_rows, tb_cols, C);
+		if (pl.k != k || pl.rows.npieces < 2) return 1;
+		lp->rows[l] = pl.rows;
+		if (l == 0) lp->cols = pl.cols;
+	}
+	return C;
+}
+
+/* launch(stream, s, r0, r1, j0, j1, outer): stream 0..C-1 = lane, C..2C-1 = the chain of boundary b = stream - C; rows are
+ * slab rows (r1 may exceed nx: the outer boundary wraps); outer = 1 for the launches of the last boundary.
+ * event(kind, b_or_lane): 0 = lane finished its tiles of this column piece, 1 = chain b is about to start this column piece
+ * (needs lanes b and b+1), 2 = chain b finished it. */
+template <typename L, typename E> int tb_lanes_walk(const LanePlan &lp, int kk, L launch, E event)
+{
+	int rc;
+	const int C = lp.C;
+	for (int ci = 0; ci < lp.cols.npieces; ci++) {
+		for (int l = 0; l < C; l++) {
+			const TbAxis &rows = lp.rows[l];
+			for (int ri = 0; ri < rows.npieces; ri++) {
+				if (rows.piece[ri].type == TB_INVERTED) continue;
+				for (int s = 0; s < kk; s++) {
+					int r0, r1, j0, j1;
+					tb_range(rows, rows.piece[ri], s, &r0, &r1);
+					tb_range(lp.cols, lp.cols.piece[ci], s, &j0, &j1);
+					if (r1 <= r0 || j1 <= j0) continue;
+					if (lp.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
+					if ((rc = launch(l, s, lp.base[l] + r0, lp.base[l] + r1, j0, j1, 0))) return rc;
+				}
+			}
+			if ((rc = event(0, l))) return rc;
+		}
+		for (int b = 0; b < C; b++) {
+			const TbAxis &rows = lp.rows[b];
+			if ((rc = event(1, b))) return rc;
+			for (int s = 0; s < kk; s++) {
+				int r0, r1, j0, j1;
+				tb_range(rows, rows.piece[rows.npieces - 1], s, &r0, &r1);
+				tb_range(lp.cols, lp.cols.piece[ci], s, &j0, &j1);
+				if (r1 <= r0 || j1 <= j0) continue;
+				if (lp.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
+				if ((rc = launch(C + b, s, lp.base[b] + r0, lp.base[b] + r1, j0, j1, b == C - 1))) return rc;
+			}
+			if ((rc = event(2, b))) return rc;
+		}
+	}
+	return 0;
+}
+
+int ensure_lanes(lbm_ctx *c)
+{
+	if (c->lanes_ready) return LBM_OK;
+	for (int k = 0; k < LBM_MAX_CHAINS; k++) {
+		if (k > 0) CK(cudaStreamCreateWithFlags(&c->lane_stream[k], cudaStreamNonBlocking));
+		CK(cudaStreamCreateWithFlags(&c->chain_stream[k], cudaStreamNonBlocking));
+		CK(cudaEventCreateWithFlags(&c->ev_lane[k], cudaEventDisableTiming));
+		CK(cudaEventCreateWithFlags(&c->ev_chain[k], cudaEventDisableTiming));
+	}
+	CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+	c->lanes_ready = 1;
+	return LBM_OK;
+}
+
+inline cudaStream_t lane_st(lbm_ctx *c, int l) { return l == 0 ? c->stream[0] : c->lane_stream[l]; }
+inline cudaStream_t chain_st(lbm_ctx *c, int b, int C) { return b == C - 1 ? c->stream[1] : c->chain_stream[b]; }
+
+/* fork: every stream first waits for what stream 0 holds so far; join: stream 0 ends up behind everything enqueued here */
+int enqueue_macro_lanes(lbm_ctx *c, int t0, int kk, const LanePlan &lp, int nsteps, bool fork, bool join)
+{
+	const bool flags = c->sync_mode == SYNC_FLAGS;
+	const int C = lp.C;
+	cudaError_t ce = cudaSuccess;
+	if (fork) {
+		CK(cudaEventRecord(c->ev_fork, c->stream[0]));
+		for (int l = 1; l < C; l++) CK(cudaStreamWaitEvent(lane_st(c, l), c->ev_fork, 0));
+		for (int b = 0; b < C; b++) CK(cudaStreamWaitEvent(chain_st(c, b, C), c->ev_fork, 0));
+	}
+	int rc = tb_lanes_walk(lp, kk,
+		[&](int st, int s, int r0, int r1, int j0, int j1, int outer) {
+			int r;
+			const int tail = t0 + s != nsteps - 1;
+			cudaStream_t q = st < C ? lane_st(c, st) : chain_st(c, st - C, C);
+			if (!(outer && flags)) return launch_step(c, (t0 + s) & 1, r0, r1, tail, q, j0, j1, tb_hint(c, s, kk));
+			if (seam_fusable(c)) return launch_step(c, (t0 + s) & 1, r0, r1, tail, q, j0, j1, tb_hint(c, s, kk), 1);
+			if ((r = launch_wait(c, q))) return r;
+			if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, q, j0, j1, tb_hint(c, s, kk)))) return r;
+			return launch_signal(c, q);
+		},
+		[&](int kind, int i) {
+			if (kind == 0) ce = cudaEventRecord(c->ev_lane[i], lane_st(c, i));
+			else if (kind == 1) {
+				ce = cudaStreamWaitEvent(chain_st(c, i, C), c->ev_lane[i], 0);
+				if (ce == cudaSuccess) ce = cudaStreamWaitEvent(chain_st(c, i, C), c->ev_lane[(i + 1) % C], 0);
+			} else ce = cudaEventRecord(c->ev_chain[i], chain_st(c, i, C));
+			return ce == cudaSuccess ? 0 : (int)LBM_ERR_CUDA;
+		});
+	if (ce != cudaSuccess) return fail(LBM_ERR_CUDA, "enqueue_macro_lanes: %s", cudaGetErrorString(ce));
+	if (rc) return rc;
+	for (int l = 0; l < C; l++) {                                /* the next macro-step's tiles of a lane need its two seam chains */
+		CK(cudaStreamWaitEvent(lane_st(c, l), c->ev_chain[l], 0));
+		CK(cudaStreamWaitEvent(lane_st(c, l), c->ev_chain[(l + C - 1) % C], 0));
+	}
+	if (join)
+		for (int l = 1; l < C; l++) {
+			CK(cudaEventRecord(c->ev_lane[l], lane_st(c, l)));
+			CK(cudaStreamWaitEvent(c->stream[0], c->ev_lane[l], 0));
+		}
+	return LBM_OK;
+}
+
 int run_wavefront(lbm_ctx *c, int nsteps)
 {
 	int rc;
 	static thread_local TbPlan pl;                               /* ~25 KB: not on the stack of every call */
-	tb_plan(&pl, c->nxl, c->ny, c->ldy, c->inplace && c->vw > 1 && c->nyvec == c->ny, c->sync_mode == SYNC_FLAGS,
-	        c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
+	static thread_local LanePlan lp;
+	const int strips_ok = c->inplace && c->vw > 1 && c->nyvec == c->ny;
+	tb_plan(&pl, c->nxl, c->ny, c->ldy, strips_ok, c->sync_mode == SYNC_FLAGS, c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
 	const int k = pl.k;
 	if (k < 2) {
 		for (int t = 0; t < nsteps; t++)
 			if ((rc = enqueue_step(c, t & 1, t != nsteps - 1))) return rc;
 		return LBM_OK;
 	}
+	/* concurrent chains need the in-place vector kernels on every column (a launch is then one kernel) */
+	const int C = strips_ok ? tb_plan_lanes(&lp, c->nxl, c->ny, c->ldy, strips_ok, c->sync_mode == SYNC_FLAGS, k, c->tune.tb_rows, c->tune.tb_cols, c->tune.tb_chains) : 1;
+	if (C >= 2 && (rc = ensure_lanes(c))) return rc;
+	auto macro = [&](int t0, int kk, int ns, bool fork, bool join) {
+		return C >= 2 ? enqueue_macro_lanes(c, t0, kk, lp, ns, fork, join) : enqueue_macro(c, t0, kk, pl, ns);
+	};
 	int t = 0;
 	struct Scope { lbm_ctx *c; Scope(lbm_ctx *c_) : c(c_) { c->in_wavefront = 1; } ~Scope() { c->in_wavefront = 0; } } scope(c);
 	if (c->tune.graph > 0 && nsteps - k >= k && c->sync_mode == SYNC_SELF) {      /* slabs: the epochs of wait/signal change per launch */
@@ -728,7 +890,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 			cudaGraph_t g = nullptr;
 			CK(cudaStreamBeginCapture(c->stream[0], cudaStreamCaptureModeThreadLocal));
 			const long long l0 = c->launches;
-			rc = enqueue_macro(c, 0, k, pl, 1 << 30);            /* every level with its tail source */
+			rc = macro(0, k, 1 << 30, true, true);               /* every level with its tail source */
 			c->wf_launches = c->launches - l0;
 			c->launches = l0;
 			cudaError_t e = cudaStreamEndCapture(c->stream[0], &g);
@@ -743,9 +905,11 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 			c->launches += c->wf_launches;
 		}
 	}
+	bool first = true;
 	while (t < nsteps) {
 		const int kk = nsteps - t < k ? nsteps - t : k;          /* even; pyramid bases >= 2k >= 2kk */
-		if ((rc = enqueue_macro(c, t, kk, pl, nsteps))) return rc;
+		if ((rc = macro(t, kk, nsteps, first, t + kk >= nsteps))) return rc;
+		first = false;
 		t += kk;
 	}
 	return LBM_OK;
@@ -1250,6 +1414,8 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.hints < 0 || n.hints > 3 || (n.hints > 1 && !c->inplace)) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
+	if (n.tb_chains < 0 || n.tb_chains > LBM_MAX_CHAINS) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_chains %d", n.tb_chains);
+	if (n.tb_chains == 0) n.tb_chains = 1;
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
 	if (n.tb_rows < 0 || n.tb_cols < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d, tb_cols %d", n.tb_rows, n.tb_cols);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
@@ -1292,6 +1458,34 @@ int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb
 		n++;
 		return 0;
 	});
+	return n;
+}
+
+/* The launch list of one macro-step with `chains` concurrent tile chains, in enqueue order (which is also a valid sequential
+ * order): 7 ints per launch -- level, r0, r1, j0, j1, stream, outer.  stream 0..C-1 = the lanes, C..2C-1 = the seam chains of the
+ * boundaries after lane (stream - C); a chain's launches of one column piece start after lanes b and b+1 have finished their
+ * tiles of that piece; outer = 1: the boundary between the last lane and the first (periodic wrap / slab seam).
+ * Returns the number of launches, *chains_used < 2 when the lattice is too low for lanes (use lbm_tb_schedule then). */
+int lbm_tb_schedule_chains(int nx, int ny, int multi, int chains, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *chains_used, int *launches, int cap)
+{
+	if (nx < 1 || ny < 2 || tb_depth < 0 || tb_rows < 0 || tb_cols < 0 || chains < 1 || multi < 0 || multi > 1 || (cap > 0 && !launches)) { fail(LBM_ERR_ARG, "lbm_tb_schedule_chains: bad argument"); return -1; }
+	const int per128 = 128 / (int)sizeof(real_t);
+	const int ldy = ((ny + per128 - 1) / per128) * per128;
+	static thread_local TbPlan pl;
+	static thread_local LanePlan lp;
+	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi == 1, tb_depth, tb_rows, tb_cols);
+	if (depth_used) *depth_used = pl.k;
+	const int C = (pl.k >= 2 && ny % VECWIDTH == 0) ? tb_plan_lanes(&lp, nx, ny, ldy, 1, multi == 1, pl.k, tb_rows, tb_cols, chains) : 1;
+	if (chains_used) *chains_used = C;
+	if (C < 2) return 0;
+	int n = 0;
+	tb_lanes_walk(lp, lp.k,
+		[&](int st, int s, int r0, int r1, int j0, int j1, int outer) {
+			if (n < cap) { int *o = launches + 7 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; o[5] = st; o[6] = outer; }
+			n++;
+			return 0;
+		},
+		[&](int, int) { return 0; });
 	return n;
 }
 

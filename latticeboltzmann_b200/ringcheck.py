@@ -23,7 +23,10 @@ def ring_cases(world):
             # row pyramid take whole-slab launches per event
             ("dp", "p2p", 803, 2000, dict(tb_depth=4, tb_rows=50, tb_cols=0)), ("sp", "p2p", 803, 2000, dict(tb_depth=6, tb_rows=0, tb_cols=256)),
             ("dp", "p2p", 803, 2000, dict(tb_depth=16, tb_rows=33, tb_cols=512, vec=1)), ("dp", "p2p", world, 64, dict(tb_depth=2, tb_rows=0, tb_cols=0)),
-            ("sp", "p2p", 2 * world + 1, 264, dict(tb_depth=4, tb_rows=0, tb_cols=64)), ("dp", "p2p", 7 * world + 3, 520, dict(tb_depth=4, tb_rows=2, tb_cols=104))]
+            ("sp", "p2p", 2 * world + 1, 264, dict(tb_depth=4, tb_rows=0, tb_cols=64)), ("dp", "p2p", 7 * world + 3, 520, dict(tb_depth=4, tb_rows=2, tb_cols=104)),
+            # + concurrent tile chains inside every slab (lanes on their own streams; the slab seam is the last lane boundary)
+            ("dp", "p2p", 803, 2000, dict(tb_depth=4, tb_rows=20, tb_cols=0, tb_chains=2)),
+            ("sp", "p2p", 803, 2000, dict(tb_depth=6, tb_rows=0, tb_cols=256, tb_chains=3))]
 
 
 def ring_inputs(prec, nx, ny):

@@ -55,7 +55,10 @@ ENGINES = {"default": {}, "pdl": dict(pdl=1), "graph": dict(graph=3), "graph+pdl
            # 2-D tiles: column strips as well as row bands (falls back to bands where ny is not a multiple of 8);
            # hints: the last level of every macro-step stores with the evict-first policy
            "inplace+tb2d": dict(inplace=1, tb_depth=4, tb_rows=16, tb_cols=256, graph=1, pdl=1),
-           "inplace+tb2d+hints": dict(inplace=1, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1, hints=1, vec=2)}
+           "inplace+tb2d+hints": dict(inplace=1, tb_depth=6, tb_rows=9, tb_cols=64, pdl=1, hints=3, vec=2),
+           # concurrent tile chains: the rows cut into lanes on their own streams, seam chains between them (graph: a multi-stream capture)
+           "inplace+tb+chains": dict(inplace=1, tb_depth=4, tb_rows=3, tb_chains=2, pdl=1),
+           "inplace+tb2d+chains+graph": dict(inplace=1, tb_depth=4, tb_rows=9, tb_cols=64, tb_chains=3, graph=1, pdl=1)}
 
 
 def _split(engine_kw):
@@ -69,7 +72,7 @@ def _split(engine_kw):
 @pytest.mark.parametrize("name", list(cases.CASES))
 def test_cuda_matches_reference_golden(name, engine):
     c, g = cases.CASES[name], GOLDEN[name]
-    if engine in ("pdl", "graph", "hints", "inplace+tb2d", "inplace+tb2d+hints") and c["steps"] > 1000:
+    if engine in ("pdl", "graph", "hints", "inplace+tb2d", "inplace+tb2d+hints", "inplace+tb2d+chains+graph") and c["steps"] > 1000:
         pytest.skip("10,000-step cases: not under the plain pdl/graph engines, nor under the deliberately tiny 2-D tiles "
                     "(tens of millions of launches); the in-place defaults cover temporal blocking at full length")
     fA, walls = cases.make_inputs(name)

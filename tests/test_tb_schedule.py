@@ -197,3 +197,95 @@ def test_full_size_schedules_are_valid_products(nx, ny, depth, prec):
     _axis_check(nx, k, row_pieces_of[0])
     area = sum((r1 - r0) * ((j1 - j0) if j1 > j0 else ny) for _, r0, r1, j0, j1 in launches)
     assert area == k * nx * ny
+
+
+# ---------------------------------------------------------------------------------------------------
+# concurrent tile chains (lbm_tuning.tb_chains): lanes of one slab on their own streams, seam chains between them.
+# What orders them (enqueue_macro_lanes): each stream is in order; the chain of boundary b takes a column piece only after
+# lanes b and b+1 have finished their tiles of that piece; a lane starts the next macro-step only after its two chains.
+# ---------------------------------------------------------------------------------------------------
+CHAIN_CASES = [  # nx, ny, chains, depth, rows, cols
+    (400, 4000, 2, 16, 0, 0), (96, 264, 2, 4, 9, 64), (120, 520, 3, 6, 0, 104), (200, 2048, 4, 8, 10, 512), (80, 136, 2, 16, 0, 0),
+    (64, 64, 2, 4, 0, 0), (401, 1000, 3, 32, 20, 0),
+]
+
+
+def _pieces(launches, C):
+    """split the enqueue-ordered list into (column piece, stream) segments: a new column piece begins whenever lane 0 comes
+    back after a chain launch"""
+    piece, out, seen_chain = 0, [], False
+    for l in launches:
+        st = l[5]
+        if st >= C:
+            seen_chain = True
+        elif st == 0 and seen_chain:
+            piece, seen_chain = piece + 1, False
+        out.append((piece, l))
+    return out
+
+
+@pytest.mark.parametrize("nx,ny,chains,depth,rows,cols", CHAIN_CASES)
+@pytest.mark.parametrize("prec", ["dp", "sp"])
+def test_chain_schedule_is_a_valid_sequential_order(nx, ny, chains, depth, rows, cols, prec):
+    from latticeboltzmann_b200.solver import tb_schedule_chains
+    k, C, launches = tb_schedule_chains(nx, ny, chains, depth, rows, cols, prec)
+    assert k == depth and 2 <= C <= chains
+    _check(nx, ny, k, [l[:5] for l in launches])
+    assert {l[5] for l in launches} == set(range(2 * C))
+    assert all((l[6] == 1) == (l[5] == 2 * C - 1) for l in launches)          # only the last boundary is the outer one
+    lanes_rows = [sorted({r for l in launches if l[5] == s for r in range(l[1], l[2])}) for s in range(C)]
+    for a in range(C):                                  # lanes own disjoint row ranges
+        for b in range(a + 1, C):
+            assert not set(lanes_rows[a]) & set(lanes_rows[b])
+
+
+def test_too_low_for_lanes_falls_back():
+    from latticeboltzmann_b200.solver import tb_schedule_chains
+    k, C, launches = tb_schedule_chains(60, 264, 2, 16)          # two lanes of 30 rows cannot hold a 16-level pyramid
+    assert C == 1 and launches == []
+    k, C, launches = tb_schedule_chains(200, 264, 4, 16)         # 2k + 4 = 36 rows per lane: five would fit, four were asked for
+    assert C == 4
+
+
+@pytest.mark.parametrize("nx,ny,chains,depth,rows,cols", CHAIN_CASES)
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_chain_schedule_under_concurrency(nx, ny, chains, depth, rows, cols, seed):
+    """Any interleaving of the 2C in-order streams that respects the two event rules must respect the 3x3 dependencies."""
+    from latticeboltzmann_b200.solver import tb_schedule_chains
+    k, C, launches = tb_schedule_chains(nx, ny, chains, depth, rows, cols, "dp")
+    tagged = _pieces(launches, C)
+    queues = [[(pc, l) for pc, l in tagged if l[5] == s] for s in range(2 * C)]
+    npieces = tagged[-1][0] + 1
+    # lane_done[l][pc]: number of launches of lane l belonging to pieces <= pc
+    lane_upto = [[sum(1 for p, _ in queues[l] if p <= pc) for pc in range(npieces)] for l in range(C)]
+    pos = [0] * (2 * C)
+    level = np.zeros((nx, ny), dtype=np.int16)
+    rng = np.random.default_rng(seed)
+    total = len(launches)
+    done = 0
+    while done < total:
+        ready = []
+        for s in range(2 * C):
+            if pos[s] >= len(queues[s]):
+                continue
+            pc, l = queues[s][pos[s]]
+            if s >= C:                                  # chain of boundary b: lanes b and b+1 have finished piece pc
+                b = s - C
+                if pos[b] < lane_upto[b][pc] or pos[(b + 1) % C] < lane_upto[(b + 1) % C][pc]:
+                    continue
+            ready.append(s)
+        assert ready, "deadlock"
+        s = int(rng.choice(ready))
+        pc, (lv, r0, r1, j0, j1, _, _) = queues[s][pos[s]]
+        if j0 == j1 == 0:
+            j1 = ny
+        rws, cls = np.arange(r0, r1) % nx, np.arange(j0, j1) % ny
+        assert (level[np.ix_(rws, cls)] == lv).all(), f"stream {s} level {lv} rows [{r0},{r1}) out of order"
+        for di in (-1, 0, 1):
+            for dj in (-1, 0, 1):
+                assert (level[np.ix_((rws + di) % nx, (cls + dj) % ny)] >= lv).all(), \
+                    f"stream {s} level {lv} rows [{r0},{r1}) cols [{j0},{j1}): neighbour ({di:+d},{dj:+d}) behind"
+        level[np.ix_(rws, cls)] = lv + 1
+        pos[s] += 1
+        done += 1
+    assert (level == k).all()
