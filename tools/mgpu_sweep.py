@@ -1,4 +1,4 @@
-"""Round 2, torchrun: weak-scaling unit per GPU over N GPUs, MLUPS over strip width / depth / hints of the slab schedule
+"""Round 2, torchrun: weak-scaling unit per GPU over N GPUs, MLUPS over strip width / hints / concurrent chains of the slab schedule
 (the seam chain costs one handshake per strip and level).  usage (torchrun): mgpu_sweep.py [dp|sp|both]"""
 import json
 import os
@@ -29,9 +29,10 @@ for prec in precs:
     R = 8 if prec == "dp" else 4
     dl = DistributedLattice(nx, ny, prec, device=local, inplace=True)
     dl.lat.InitializeArrays(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=min(nx, ny) // 10)
-    combos = [(16, 0, 0)] + [(k, w, h) for k in (16, 32) for w in (8192 // R, 16384 // R, 32768 // R, 65536 // R) for h in (0, 1)]
-    for k, w, hints in combos:
-        dl.lat.set_tuning(tb_depth=k, tb_cols=w, hints=hints)
+    combos = [(16, 0, 0, 1), (16, 0, 0, 2), (16, 0, 3, 2), (16, 16384 // R, 0, 1), (16, 16384 // R, 0, 2), (16, 16384 // R, 3, 2),
+              (16, 0, 0, 3), (16, 16384 // R, 0, 3), (16, 65536 // R, 0, 2)]
+    for k, w, hints, chains in combos:
+        dl.lat.set_tuning(tb_depth=k, tb_cols=w, hints=hints, tb_chains=chains)
         dist.barrier()
         dl.run_timed(k)
         best = 1e9
@@ -39,7 +40,7 @@ for prec in precs:
             torch.cuda.synchronize(); dist.barrier()
             best = min(best, mx(dl.run_timed(T)))
         if rank == 0:
-            print(json.dumps(dict(prec=prec, gpus=world, k=k, W=w, hints=hints, mlups=round(nx * ny * T / best / 1e3, 1),
+            print(json.dumps(dict(prec=prec, gpus=world, k=k, W=w, hints=hints, chains=chains, mlups=round(nx * ny * T / best / 1e3, 1),
                                   per_gpu=round(nx * ny * T / best / 1e3 / world, 1))), flush=True)
     dl.close()
     dist.barrier()
