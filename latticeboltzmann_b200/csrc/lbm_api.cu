@@ -300,7 +300,10 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		const double band = sizeof(real_t) == 8 ? 45e6 : 60e6;
 		/* SP: vec 4 and k = 16 since the SP kernels run at 64 registers -- 800x4000 105.7 GLUPS against 98.7 for the
 		 * earlier vec 2 / k = 8, 1600x4000 109.9 against 101.9 (profiles/r01_run28) */
-		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) c->tune.tb_depth = k;
+		if (row_bytes * c->nxl > 64e6 && band / row_bytes - k >= 64 && c->nxl >= 2 * k + 2) {
+			c->tune.tb_depth = k;
+			c->tune.tb_chains = 2;                               /* DP 400x4000 54.1 -> 65.1 GLUPS, 800x4000 55.6 -> 67.1 (profiles/r02_run7) */
+		}
 	}
 	*out = c;
 	return LBM_OK;

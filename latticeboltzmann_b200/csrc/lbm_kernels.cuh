@@ -234,48 +234,6 @@ __device__ __forceinline__ void collide_vec_order(const T (&f)[9], T (&o)[9], co
 	}
 }
 
-// Two fluid sites at once, SP only: collide_vec_order() on the packed FP32x2 pipe of sm_100 (FADD2 / FMUL2 / FFMA2: one issue
-// slot for two sites).  Every packed operation rounds each half exactly like its scalar _rn counterpart, the operation order is
-// the one above, and the two rewrites are exact identities: a - b is taken as fma(b, -1, a) (the product is exact, one rounding),
-// and 1 + ((-e) + t) as 1 + (t - e), with t = 0.5*(e*e) - usq shared by the speeds e and -e.  Not for mixed groups (the
-// caller takes the scalar path when the aligned VECWIDTH group holds a wall).
-__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
-__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
-__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a); }
-__device__ __forceinline__ float2 dup2(float a) { return make_float2(a, a); }
-__device__ __forceinline__ void collide_vec_order_x2(const float2 (&f)[9], float2 (&o)[9], const StepParams<float> &p)
-{
-	float2 rho = add2(dup2(0.0f), f[0]);                         // LB.c:360,372
-#pragma unroll
-	for (int s = 1; s < 9; s++) rho = add2(rho, f[s]);           // LB.c:373-380
-	float2 ux = add2(f[6], f[2]);                                // LB.c:382-387
-	ux = add2(ux, f[5]); ux = sub2(ux, f[7]); ux = sub2(ux, f[4]); ux = sub2(ux, f[8]);
-	ux = make_float2(__fdiv_rn(ux.x, rho.x), __fdiv_rn(ux.y, rho.y));
-	float2 uy = add2(f[5], f[1]);                                // LB.c:389-394
-	uy = add2(uy, f[8]); uy = sub2(uy, f[6]); uy = sub2(uy, f[3]); uy = sub2(uy, f[7]);
-	uy = make_float2(__fdiv_rn(uy.x, rho.x), __fdiv_rn(uy.y, rho.y));
-	const float2 usq = mul2(dup2(1.5f), add2(mul2(ux, ux), mul2(uy, uy)));   // LB.c:397
-	ux = mul2(ux, dup2(3.0f));                                   // LB.c:400-401
-	uy = mul2(uy, dup2(3.0f));
-	const float2 sum = add2(ux, uy), dif = sub2(ux, uy);
-	const float2 one = dup2(1.0f), half = dup2(0.5f);
-	const float2 ty = sub2(mul2(half, mul2(uy, uy)), usq), tx = sub2(mul2(half, mul2(ux, ux)), usq);
-	const float2 ts = sub2(mul2(half, mul2(sum, sum)), usq), td = sub2(mul2(half, mul2(dif, dif)), usq);
-	float2 q[9];
-	q[0] = sub2(one, usq);                                       // LB.c:413
-	q[1] = add2(one, add2(uy, ty));   q[3] = add2(one, sub2(ty, uy));     // LB.c:414-421
-	q[2] = add2(one, add2(ux, tx));   q[4] = add2(one, sub2(tx, ux));
-	q[5] = add2(one, add2(sum, ts));  q[7] = add2(one, sub2(ts, sum));
-	q[6] = add2(one, add2(dif, td));  q[8] = add2(one, sub2(td, dif));
-	const float2 r0 = mul2(dup2(p.w0), rho), r14 = mul2(dup2(p.w14), rho), r58 = mul2(dup2(p.w58), rho);   // LB.c:425-433
-	const float2 itau = dup2(p.itau);
-#pragma unroll
-	for (int s = 0; s < 9; s++) {
-		q[s] = mul2(q[s], s == 0 ? r0 : (s <= 4 ? r14 : r58));
-		o[s] = add2(f[s], mul2(itau, sub2(q[s], f[s])));         // LB.c:442-450
-	}
-}
-
 // Fluid site, rounding order of the scalar function StreamCollide LB.c:257-297.
 template <typename T>
 __device__ __forceinline__ void collide_scalar_order(const T (&f)[9], T (&o)[9], const StepParams<T> &p)
@@ -365,30 +323,6 @@ __device__ __forceinline__ uint32_t relax_sites(const StepParams<T> &p, const T 
 		sx = (__ldg(p.slip + w) >> sh) & bits;
 		sy = (__ldg(p.slip + (size_t)p.nxl * p.ldw + w) >> sh) & bits;
 	}
-#ifndef LBM_NO_F32X2
-	if constexpr (sizeof(T) == 4 && V >= 2) {                // SP, no wall in my sites nor in my aligned group: two sites per FP32x2 op
-		if (bits == 0u && !dbl) {
-#pragma unroll
-			for (int k = 0; k < V; k += 2) {
-				float2 fk[9], ok[9];
-#pragma unroll
-				for (int s = 0; s < 9; s++) fk[s] = make_float2(f[s][k], f[s][k + 1]);
-				collide_vec_order_x2(fk, ok, p);
-#pragma unroll
-				for (int s = 0; s < 9; s++) { o[s][k] = ok[s].x; o[s][k + 1] = ok[s].y; }
-			}
-			if (j0 == 0 && tail_source) {
-				T o0[9];
-#pragma unroll
-				for (int s = 0; s < 9; s++) o0[s] = o[s][0];
-				source_site<T>(o0, p);
-#pragma unroll
-				for (int s = 0; s < 9; s++) o[s][0] = o0[s];
-			}
-			return bits;
-		}
-	}
-#endif
 #pragma unroll
 	for (int k = 0; k < V; k++) {
 		T fk[9], ok[9];

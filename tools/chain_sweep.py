@@ -1,6 +1,7 @@
 """Round 2: concurrent tile chains (lbm_tuning.tb_chains) inside ONE context: chains x tile budget per chain x hints, on the
 weak-scaling unit and on the small temporally blocked lattices (CUDA-graph path).  Every point restarts from the same initial
-state and must end with the checksum of the single-chain run.   usage: chain_sweep.py [dp|sp|both] [large|small|all]"""
+state and must end with the checksum of the single-chain run.   `resident`: lattices that fit in L2 whole (no temporal blocking by default): one launch per step against 16-level macro-steps of 2-3
+chains.   usage: chain_sweep.py [dp|sp|both] [large|small|resident|all]"""
 import json
 import os
 import sys
@@ -19,13 +20,18 @@ for prec in precs:
         lattices.append((8192, 32768, 64))
     if which in ("small", "all"):
         lattices += [(400, 4000, 1600), (800, 4000, 800)]
+    if which in ("resident", "all"):
+        lattices += [(400, 2000, 3200)] if prec == "dp" else [(400, 4000, 1600), (400, 2000, 3200)]
     for nx, ny, T in lattices:
         k = 16
         with Lattice(nx, ny, prec, inplace=True) as lat:
             sc = dict(bar_i0=0, bar_i1=0, disc_ci=nx // 2, disc_cj=ny // 5, disc_r=min(nx, ny) // 10, perturb_seed=7, perturb_amp=0.05)
             base = lat.get_tuning()
+            resident = 9 * R * nx * ny <= 60e6
             combos = [(1, 0, 0)]
-            for C in (2, 3, 4):
+            if resident and which in ("resident", "all"):
+                combos = [(0, 0, 0), (1, 0, ny), (2, 0, ny), (3, 0, ny), (2, 60, ny), (2, 40, ny)]      # chains 0: tb off (the default there)
+            for C in (() if resident else (2, 3, 4)):
                 combos.append((C, 0, 0))
                 if nx >= 8192:
                     w = 16384 // R
@@ -42,7 +48,7 @@ for prec in precs:
             for C, h, w in combos:
                 for hints in ((0, 3) if (C <= 2 and h == 0) else (0,)):
                     lat.InitializeArrays(**sc)
-                    lat.set_tuning(**{**base, "tb_depth": k, "tb_chains": C, "tb_rows": h, "tb_cols": w, "hints": hints})
+                    lat.set_tuning(**{**base, "tb_depth": k if C else 0, "tb_chains": max(C, 1), "tb_rows": h, "tb_cols": w, "hints": hints})
                     lat.run_timed(k)
                     lat.InitializeArrays(**sc)
                     ms = lat.run_timed(T)
