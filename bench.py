@@ -25,7 +25,7 @@ roofline  the dominant kernel's algorithmic bytes (2*9*sizeof(real) per site upd
           MEASURED_PEAKS.json hbm_gbs) is reported beside it under "hbm".  The A/B engine streams the lattice through HBM
           every step: bound = "hbm".
 parity    config.parity: before anything is timed at N >= 2 the ring-parity pass (latticeboltzmann_b200/ringcheck.py: the
-          slab ring over the N GPUs == the single-GPU lattice, bit for bit, 15 cases) and a cross-engine checksum of the timed
+          slab ring over the N GPUs == the single-GPU lattice, bit for bit, 17 cases) and a cross-engine checksum of the timed
           lattice (in place + temporal blocking vs A/B: two independent engines); at N = 1 the golden digests of the
           compiled reference for configs[1], configs[2] (through the e2e path) and the same cross-engine checksum.
 cpu_baseline / --impl reference = the reference's own AVX+OpenMP build (oracle/_ref, Makefile:2 flags), timed by its own
@@ -436,9 +436,9 @@ def bench_single(args):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": headline_workload(1), "lattice": f"{nx}x{ny}", "timesteps_per_step": T,
                        "scene": "channel walls + disc obstacle (InitializeArrays closed form), tau 0.7, accel 0.005",
-                       "engine": "in-place single buffer (lbm_config.inplace=1, AA kernels) + 2-D temporal blocking in L2 (library defaults); "
+                       "engine": "in-place single buffer (lbm_config.inplace=1, AA kernels) + 2-D temporal blocking in L2, two concurrent tile chains (library defaults); "
                                  "the A/B double-buffer engine of the same library is under 'ab_double_buffer'",
-                       "l2": "19.3 GB lattice, far larger than L2: nothing is flushed because keeping ~60 MB tiles L2-resident for 16 timesteps IS the "
+                       "l2": "19.3 GB lattice, far larger than L2: nothing is flushed because keeping two 24 MB (SP: 36 MB) tiles L2-resident for 16 timesteps IS the "
                              "engine (HBM sees each site once per several steps; the roof that binds is L2 bandwidth, see roofline)",
                        "parity": ("bit-exact: " if ok else "NOT CLEAN: ") + "; ".join(parity),
                        "skipped": skipped},
