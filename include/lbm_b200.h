@@ -236,7 +236,7 @@ typedef struct {
 	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
 	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 16 KB
 	                     row segments, 32 KB on slabs, only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
-	int tb_chains;    /* concurrent tile chains of the temporal-blocking schedule (1..4; 0 = 1): the slab's rows are cut into this many
+	int tb_chains;    /* concurrent tile chains of the temporal-blocking schedule (1..4; 0 = the default, 2): the slab's rows are cut into this many
 	                     lanes that run their tiles on separate streams, each with its share of the L2 tile budget, the boundaries
 	                     between lanes handled like slab seams.  A second chain fills the drain every tile level pays. */
 } lbm_tuning;

@@ -631,7 +631,7 @@ void tb_axis(TbAxis *ax, int n, int g, int e, int k, int P)
 /* multi != 0: this slab is one of several.  Every slab of a ring must then walk the SAME sequence of (column piece,
  * level) events, so the depth is never clamped to the slab: a slab too low for the row pyramid (2k + 2 > nx)
  * takes whole-slab launches per event instead of row pieces. */
-void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols, int chains = 1)
+void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols, int chains = 1, int chains_asked = 1)
 {
 	const int edge = multi != 0 || chains > 1;                  /* first and last row belong to the seam piece (a slab of a ring, a lane) */
 	const int G = 8;                                             /* column skew per level: keeps every vector width aligned */
@@ -646,8 +646,11 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int 
 	double budget = sizeof(real_t) == 8 ? 45e6 : 60e6;
 	int W = tb_cols;
 	if (!strips_ok || ny % G || 2 * G * k + G > ny) W = ny;      /* strips need aligned, wide enough rows */
-	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)((multi ? 32768 : 16384) / sizeof(real_t));   /* slabs: fewer, wider
-	                                                                  strips -- every (strip, level) costs a handshake with both neighbours */
+	else if (W == 0) W = budget / (cell * ldy) - k >= 64 ? ny : (int)(((multi && chains_asked < 2) ? 32768 : 16384) / sizeof(real_t));   /* single-chain
+	                                                                  slabs: fewer, wider strips -- every (strip, level) costs a handshake with both
+	                                                                  neighbours; with lanes 16 KB segments win on slabs too (profiles/r02_run8_2gpu).
+	                                                                  chains_asked, not the lanes this slab has room for: every slab of a ring must
+	                                                                  cut the same strips */
 	if (W >= ny) {
 		pl->cols.n = ny; pl->cols.g = G; pl->cols.e = 0; pl->cols.npieces = 1;
 		pl->cols.piece[0] = TbPiece{TB_WHOLE, 0, ny};
@@ -748,6 +751,7 @@ struct LanePlan { int k, C; int base[LBM_MAX_CHAINS + 1]; TbAxis rows[LBM_MAX_CH
 /* returns the number of lanes used (< 2: take the single-chain schedule) */
 int tb_plan_lanes(LanePlan *lp, int nx, int ny, int ldy, int strips_ok, int multi, int tb_depth, int tb_rows, int tb_cols, int chains)
 {
+	const int asked = chains;
 	static thread_local TbPlan pl;
 	int k = tb_depth & ~1;
 	if (k < 2 || chains < 2) return 1;
@@ -757,7 +761,7 @@ int tb_plan_lanes(LanePlan *lp, int nx, int ny, int ldy, int strips_ok, int mult
 	lp->k = k; lp->C = C;
 	for (int l = 0; l <= C; l++) lp->base[l] = (int)((long long)nx * l / C);
 	for (int l = 0; l < C; l++) {
-		tb_plan(&pl, lp->base[l + 1] - lp->base[l], ny, ldy, strips_ok, multi, k, tb_rows, tb_cols, C);
+		tb_plan(&pl, lp->base[l + 1] - lp->base[l], ny, ldy, strips_ok, multi, k, tb_rows, tb_cols, C, asked);
 		if (pl.k != k || pl.rows.npieces < 2) return 1;
 		lp->rows[l] = pl.rows;
 		if (l == 0) lp->cols = pl.cols;
@@ -873,7 +877,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 	static thread_local TbPlan pl;                               /* ~25 KB: not on the stack of every call */
 	static thread_local LanePlan lp;
 	const int strips_ok = c->inplace && c->vw > 1 && c->nyvec == c->ny;
-	tb_plan(&pl, c->nxl, c->ny, c->ldy, strips_ok, c->sync_mode == SYNC_FLAGS, c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols);
+	tb_plan(&pl, c->nxl, c->ny, c->ldy, strips_ok, c->sync_mode == SYNC_FLAGS, c->tune.tb_depth, c->tune.tb_rows, c->tune.tb_cols, 1, strips_ok ? c->tune.tb_chains : 1);
 	const int k = pl.k;
 	if (k < 2) {
 		for (int t = 0; t < nsteps; t++)
@@ -1418,7 +1422,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
 	if (n.tb_chains < 0 || n.tb_chains > LBM_MAX_CHAINS) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_chains %d", n.tb_chains);
-	if (n.tb_chains == 0) n.tb_chains = 1;
+	if (n.tb_chains == 0) n.tb_chains = 2;
 	if (n.tb_depth < 0 || n.tb_depth > 1024 || (n.tb_depth & 1)) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_depth %d (even, 0..1024)", n.tb_depth);
 	if (n.tb_rows < 0 || n.tb_cols < 0) return fail(LBM_ERR_ARG, "lbm_set_tuning: tb_rows %d, tb_cols %d", n.tb_rows, n.tb_cols);
 	if (n.tb_depth && !c->inplace) return fail(LBM_ERR_STATE, "lbm_set_tuning: tb_depth needs an in-place context (lbm_config.inplace): "
@@ -1476,7 +1480,7 @@ int lbm_tb_schedule_chains(int nx, int ny, int multi, int chains, int tb_depth, 
 	const int ldy = ((ny + per128 - 1) / per128) * per128;
 	static thread_local TbPlan pl;
 	static thread_local LanePlan lp;
-	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi == 1, tb_depth, tb_rows, tb_cols);
+	tb_plan(&pl, nx, ny, ldy, ny % VECWIDTH == 0, multi == 1, tb_depth, tb_rows, tb_cols, 1, chains);
 	if (depth_used) *depth_used = pl.k;
 	const int C = (pl.k >= 2 && ny % VECWIDTH == 0) ? tb_plan_lanes(&lp, nx, ny, ldy, 1, multi == 1, pl.k, tb_rows, tb_cols, chains) : 1;
 	if (chains_used) *chains_used = C;
