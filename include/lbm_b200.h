@@ -252,13 +252,10 @@ long long lbm_kernel_launches(lbm_ctx *ctx);
  * ring, 0 = lattice too small, plain stepping).  Returns the number of launches (which may exceed cap; only cap
  * entries are written), -1 on bad arguments. */
 int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *launches, int cap);
-/* The same for lbm_tuning.tb_chains > 1 (concurrent tile chains): 8 ints per launch, (level, r0, r1, j0, j1, stream, outer, tag),
- * in enqueue order, which is also a valid sequential order.  stream 0..C-1 = the lanes' own tiles, C..2C-1 = the seam chain of
- * the boundary after lane (stream - C); outer = 1 marks the boundary between the last lane and the first (the periodic wrap / the
- * slab seam); tag (lane launches): bit 0 = the lane's pyramid, bit 1 = its last parallelogram.  What orders the streams: each is
- * in order; a chain's launches of a column piece start after lanes b and b+1 have finished their tiles of that piece, except on
- * the last column piece, where the chain's level s waits only for level s-1 of lane b's last parallelogram and of lane b+1's
- * pyramid; a lane starts the next macro-step after its two chains.
+/* The same for lbm_tuning.tb_chains > 1 (concurrent tile chains): 7 ints per launch, (level, r0, r1, j0, j1, stream, outer), in
+ * enqueue order, which is also a valid sequential order.  stream 0..C-1 = the lanes' own tiles, C..2C-1 = the seam chain of the
+ * boundary after lane (stream - C), whose launches of one column piece start after lanes b and b+1 have finished their tiles of
+ * that piece; outer = 1 marks the boundary between the last lane and the first (the periodic wrap / the slab seam).
  * *chains_used < 2: the slab is too low for lanes, lbm_tb_schedule describes what runs.  Host logic only. */
 int lbm_tb_schedule_chains(int nx, int ny, int multi, int chains, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *chains_used,
                            int *launches, int cap);

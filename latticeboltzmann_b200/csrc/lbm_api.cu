@@ -102,8 +102,6 @@ struct lbm_ctx {
 	 * the boundary between lanes b and b+1 on chain_stream[b] (the outer boundary -- the periodic wrap / the slab seam -- on stream[1]) */
 	cudaStream_t lane_stream[LBM_MAX_CHAINS], chain_stream[LBM_MAX_CHAINS];
 	cudaEvent_t ev_lane[LBM_MAX_CHAINS], ev_chain[LBM_MAX_CHAINS], ev_fork;
-	std::vector<cudaEvent_t> ev_level;   // per (lane, pyramid | last parallelogram, level): the seam chains of the last column piece
-	int ev_level_depth;
 	int lanes_ready;
 #ifdef LBM_EXPERIMENTAL
 	lbm_experimental exp;
@@ -209,6 +207,7 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 	if (prop.major != 10) return fail(LBM_ERR_CUDA, "lbm_create: device is sm_%d%d, this library carries sm_100a code only", prop.major, prop.minor);
 
 	lbm_ctx *c = new lbm_ctx();
+	memset(c, 0, sizeof *c);
 	c->cfg = *cfg;
 	c->cfg.row_lo = lo; c->cfg.row_hi = hi; c->cfg.vecwidth = vw;
 	c->nxl = hi - lo;
@@ -333,7 +332,6 @@ int lbm_destroy(lbm_ctx *c)
 		if (c->ev_chain[k]) cudaEventDestroy(c->ev_chain[k]);
 	}
 	if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-	for (cudaEvent_t e : c->ev_level) cudaEventDestroy(e);
 	if (c->ev_main) cudaEventDestroy(c->ev_main);
 	if (c->ev_t0) cudaEventDestroy(c->ev_t0);
 	if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -773,52 +771,40 @@ int tb_plan_lanes(LanePlan *lp, int nx, int ny, int ldy, int strips_ok, int mult
 
 /* launch(stream, s, r0, r1, j0, j1, outer): stream 0..C-1 = lane, C..2C-1 = the chain of boundary b = stream - C; rows are
  * slab rows (r1 may exceed nx: the outer boundary wraps); outer = 1 for the launches of the last boundary.
- * event(kind, i, s) -- what orders the streams:
- *   coarse (every column piece but the last): 0 = lane i finished its tiles of this column piece; 1 = chain i is about to
- *   start this column piece (waits for lanes i and i+1); 2 = chain i finished it.
- *   fine (the last column piece, whose seam chains nothing else would run beside): 3 = lane i has launched level s of its
- *   pyramid, 4 = of its last parallelogram (the two pieces next to its boundaries); 5 = chain i is about to launch level s >= 1
- *   (waits for level s-1 of lane i's last parallelogram and of lane i+1's pyramid: all its rows [B-2-s, B+2+s) need beyond its
- *   own previous level).  Then the chain trails the lanes' last tiles by one level instead of starting after them.
- * tag passed to launch(): bit 0 = pyramid, bit 1 = last parallelogram of its lane (lane launches only). */
+ * event(kind, b_or_lane): 0 = lane finished its tiles of this column piece, 1 = chain b is about to start this column piece
+ * (needs lanes b and b+1), 2 = chain b finished it. */
 template <typename L, typename E> int tb_lanes_walk(const LanePlan &lp, int kk, L launch, E event)
 {
 	int rc;
 	const int C = lp.C;
 	for (int ci = 0; ci < lp.cols.npieces; ci++) {
-		const bool fine = ci == lp.cols.npieces - 1;
 		for (int l = 0; l < C; l++) {
 			const TbAxis &rows = lp.rows[l];
 			for (int ri = 0; ri < rows.npieces; ri++) {
 				if (rows.piece[ri].type == TB_INVERTED) continue;
-				const int tag = (ri == 0 ? 1 : 0) | (ri == rows.npieces - 2 ? 2 : 0);
 				for (int s = 0; s < kk; s++) {
 					int r0, r1, j0, j1;
 					tb_range(rows, rows.piece[ri], s, &r0, &r1);
 					tb_range(lp.cols, lp.cols.piece[ci], s, &j0, &j1);
-					if (r1 > r0 && j1 > j0) {
-						if (lp.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
-						if ((rc = launch(l, s, lp.base[l] + r0, lp.base[l] + r1, j0, j1, 0, tag))) return rc;
-					}
-					if (fine && (tag & 1) && (rc = event(3, l, s))) return rc;
-					if (fine && (tag & 2) && (rc = event(4, l, s))) return rc;
+					if (r1 <= r0 || j1 <= j0) continue;
+					if (lp.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
+					if ((rc = launch(l, s, lp.base[l] + r0, lp.base[l] + r1, j0, j1, 0))) return rc;
 				}
 			}
-			if (!fine && (rc = event(0, l, 0))) return rc;
+			if ((rc = event(0, l))) return rc;
 		}
 		for (int b = 0; b < C; b++) {
 			const TbAxis &rows = lp.rows[b];
-			if (!fine && (rc = event(1, b, 0))) return rc;
+			if ((rc = event(1, b))) return rc;
 			for (int s = 0; s < kk; s++) {
 				int r0, r1, j0, j1;
 				tb_range(rows, rows.piece[rows.npieces - 1], s, &r0, &r1);
 				tb_range(lp.cols, lp.cols.piece[ci], s, &j0, &j1);
 				if (r1 <= r0 || j1 <= j0) continue;
 				if (lp.cols.piece[ci].type == TB_WHOLE) j0 = j1 = 0;
-				if (fine && s > 0 && (rc = event(5, b, s))) return rc;
-				if ((rc = launch(C + b, s, lp.base[b] + r0, lp.base[b] + r1, j0, j1, b == C - 1, 0))) return rc;
+				if ((rc = launch(C + b, s, lp.base[b] + r0, lp.base[b] + r1, j0, j1, b == C - 1))) return rc;
 			}
-			if ((rc = event(2, b, 0))) return rc;
+			if ((rc = event(2, b))) return rc;
 		}
 	}
 	return 0;
@@ -838,19 +824,6 @@ int ensure_lanes(lbm_ctx *c)
 	return LBM_OK;
 }
 
-/* ev_level[(lane * 2 + which) * depth + level]: which 0 = the lane's pyramid, 1 = its last parallelogram */
-int ensure_level_events(lbm_ctx *c, int depth)
-{
-	const size_t need = (size_t)LBM_MAX_CHAINS * 2 * depth;
-	while (c->ev_level.size() < need) {
-		cudaEvent_t e;
-		CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-		c->ev_level.push_back(e);
-	}
-	c->ev_level_depth = depth;
-	return LBM_OK;
-}
-
 inline cudaStream_t lane_st(lbm_ctx *c, int l) { return l == 0 ? c->stream[0] : c->lane_stream[l]; }
 inline cudaStream_t chain_st(lbm_ctx *c, int b, int C) { return b == C - 1 ? c->stream[1] : c->chain_stream[b]; }
 
@@ -866,7 +839,7 @@ int enqueue_macro_lanes(lbm_ctx *c, int t0, int kk, const LanePlan &lp, int nste
 		for (int b = 0; b < C; b++) CK(cudaStreamWaitEvent(chain_st(c, b, C), c->ev_fork, 0));
 	}
 	int rc = tb_lanes_walk(lp, kk,
-		[&](int st, int s, int r0, int r1, int j0, int j1, int outer, int) {
+		[&](int st, int s, int r0, int r1, int j0, int j1, int outer) {
 			int r;
 			const int tail = t0 + s != nsteps - 1;
 			cudaStream_t q = st < C ? lane_st(c, st) : chain_st(c, st - C, C);
@@ -876,19 +849,12 @@ int enqueue_macro_lanes(lbm_ctx *c, int t0, int kk, const LanePlan &lp, int nste
 			if ((r = launch_step(c, (t0 + s) & 1, r0, r1, tail, q, j0, j1, tb_hint(c, s, kk)))) return r;
 			return launch_signal(c, q);
 		},
-		[&](int kind, int i, int s) {
-			const int D = c->ev_level_depth;
+		[&](int kind, int i) {
 			if (kind == 0) ce = cudaEventRecord(c->ev_lane[i], lane_st(c, i));
 			else if (kind == 1) {
 				ce = cudaStreamWaitEvent(chain_st(c, i, C), c->ev_lane[i], 0);
 				if (ce == cudaSuccess) ce = cudaStreamWaitEvent(chain_st(c, i, C), c->ev_lane[(i + 1) % C], 0);
-			} else if (kind == 2) ce = cudaEventRecord(c->ev_chain[i], chain_st(c, i, C));
-			else if (kind == 3) ce = cudaEventRecord(c->ev_level[(size_t)(i * 2 + 0) * D + s], lane_st(c, i));
-			else if (kind == 4) ce = cudaEventRecord(c->ev_level[(size_t)(i * 2 + 1) * D + s], lane_st(c, i));
-			else {
-				ce = cudaStreamWaitEvent(chain_st(c, i, C), c->ev_level[(size_t)(i * 2 + 1) * D + s - 1], 0);
-				if (ce == cudaSuccess) ce = cudaStreamWaitEvent(chain_st(c, i, C), c->ev_level[(size_t)(((i + 1) % C) * 2 + 0) * D + s - 1], 0);
-			}
+			} else ce = cudaEventRecord(c->ev_chain[i], chain_st(c, i, C));
 			return ce == cudaSuccess ? 0 : (int)LBM_ERR_CUDA;
 		});
 	if (ce != cudaSuccess) return fail(LBM_ERR_CUDA, "enqueue_macro_lanes: %s", cudaGetErrorString(ce));
@@ -920,7 +886,7 @@ int run_wavefront(lbm_ctx *c, int nsteps)
 	}
 	/* concurrent chains need the in-place vector kernels on every column (a launch is then one kernel) */
 	const int C = strips_ok ? tb_plan_lanes(&lp, c->nxl, c->ny, c->ldy, strips_ok, c->sync_mode == SYNC_FLAGS, k, c->tune.tb_rows, c->tune.tb_cols, c->tune.tb_chains) : 1;
-	if (C >= 2 && ((rc = ensure_lanes(c)) || (rc = ensure_level_events(c, k)))) return rc;
+	if (C >= 2 && (rc = ensure_lanes(c))) return rc;
 	auto macro = [&](int t0, int kk, int ns, bool fork, bool join) {
 		return C >= 2 ? enqueue_macro_lanes(c, t0, kk, lp, ns, fork, join) : enqueue_macro(c, t0, kk, pl, ns);
 	};
@@ -1503,11 +1469,9 @@ int lbm_tb_schedule(int nx, int ny, int multi, int tb_depth, int tb_rows, int tb
 }
 
 /* The launch list of one macro-step with `chains` concurrent tile chains, in enqueue order (which is also a valid sequential
- * order): 8 ints per launch -- level, r0, r1, j0, j1, stream, outer, tag.  stream 0..C-1 = the lanes, C..2C-1 = the seam chains of the
- * boundaries after lane (stream - C); outer = 1: the boundary between the last lane and the first (periodic wrap / slab seam);
- * tag (lane launches): bit 0 = the lane's pyramid, bit 1 = its last parallelogram.  A chain's launches of a column piece start
- * after lanes b and b+1 have finished their tiles of that piece -- except on the LAST column piece, where the chain's level s
- * waits only for level s-1 of lane b's last parallelogram and of lane b+1's pyramid (tb_lanes_walk).
+ * order): 7 ints per launch -- level, r0, r1, j0, j1, stream, outer.  stream 0..C-1 = the lanes, C..2C-1 = the seam chains of the
+ * boundaries after lane (stream - C); a chain's launches of one column piece start after lanes b and b+1 have finished their
+ * tiles of that piece; outer = 1: the boundary between the last lane and the first (periodic wrap / slab seam).
  * Returns the number of launches, *chains_used < 2 when the lattice is too low for lanes (use lbm_tb_schedule then). */
 int lbm_tb_schedule_chains(int nx, int ny, int multi, int chains, int tb_depth, int tb_rows, int tb_cols, int *depth_used, int *chains_used, int *launches, int cap)
 {
@@ -1523,12 +1487,12 @@ int lbm_tb_schedule_chains(int nx, int ny, int multi, int chains, int tb_depth, 
 	if (C < 2) return 0;
 	int n = 0;
 	tb_lanes_walk(lp, lp.k,
-		[&](int st, int s, int r0, int r1, int j0, int j1, int outer, int tag) {
-			if (n < cap) { int *o = launches + 8 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; o[5] = st; o[6] = outer; o[7] = tag; }
+		[&](int st, int s, int r0, int r1, int j0, int j1, int outer) {
+			if (n < cap) { int *o = launches + 7 * n; o[0] = s; o[1] = r0; o[2] = r1; o[3] = j0; o[4] = j1; o[5] = st; o[6] = outer; }
 			n++;
 			return 0;
 		},
-		[&](int, int, int) { return 0; });
+		[&](int, int) { return 0; });
 	return n;
 }
 

@@ -269,14 +269,13 @@ def tb_schedule(nx, ny, tb_depth, tb_rows=0, tb_cols=0, prec="dp", multi=False):
 
 def tb_schedule_chains(nx, ny, chains, tb_depth, tb_rows=0, tb_cols=0, prec="dp", multi=False):
     """Launch list of one macro-step with concurrent tile chains (lbm_tb_schedule_chains; host logic, no GPU):
-    returns (depth_used, chains_used, [(level, r0, r1, j0, j1, stream, outer, tag), ...]) in enqueue order; streams 0..C-1 are the
-    lanes, C..2C-1 the seam chains of the boundaries after lane (stream - C); tag bit 0 = a lane's pyramid, bit 1 = its last
-    parallelogram.  chains_used < 2: no lanes (see tb_schedule)."""
+    returns (depth_used, chains_used, [(level, r0, r1, j0, j1, stream, outer), ...]) in enqueue order; streams 0..C-1 are the
+    lanes, C..2C-1 the seam chains of the boundaries after lane (stream - C).  chains_used < 2: no lanes (see tb_schedule)."""
     lib = _capi.load(prec)
     k, cu = ctypes.c_int(), ctypes.c_int()
     n = lib.dll.lbm_tb_schedule_chains(nx, ny, int(bool(multi)), chains, tb_depth, tb_rows, tb_cols, ctypes.byref(k), ctypes.byref(cu), None, 0)
     if n < 0:
         raise _capi.LbmError(_capi.ERR_ARG, lib.dll.lbm_last_error().decode())
-    buf = (ctypes.c_int * (8 * max(n, 1)))()
+    buf = (ctypes.c_int * (7 * max(n, 1)))()
     lib.dll.lbm_tb_schedule_chains(nx, ny, int(bool(multi)), chains, tb_depth, tb_rows, tb_cols, ctypes.byref(k), ctypes.byref(cu), buf, n)
-    return k.value, cu.value, [tuple(buf[8 * i + m] for m in range(8)) for i in range(n)]
+    return k.value, cu.value, [tuple(buf[7 * i + m] for m in range(7)) for i in range(n)]

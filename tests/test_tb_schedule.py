@@ -250,47 +250,33 @@ def test_too_low_for_lanes_falls_back():
 @pytest.mark.parametrize("nx,ny,chains,depth,rows,cols", CHAIN_CASES)
 @pytest.mark.parametrize("seed", [0, 1, 2])
 def test_chain_schedule_under_concurrency(nx, ny, chains, depth, rows, cols, seed):
-    """Any interleaving of the 2C in-order streams that respects the event rules must respect the 3x3 dependencies.  Rules
-    (enqueue_macro_lanes): every column piece but the last -- the chain of boundary b starts after lanes b and b+1 have finished
-    their tiles of that piece; the last column piece -- the chain's level s waits only for level s-1 of lane b's last parallelogram
-    and of lane b+1's pyramid (tag bits 2 / 1) of that piece."""
+    """Any interleaving of the 2C in-order streams that respects the two event rules must respect the 3x3 dependencies."""
     from latticeboltzmann_b200.solver import tb_schedule_chains
     k, C, launches = tb_schedule_chains(nx, ny, chains, depth, rows, cols, "dp")
     tagged = _pieces(launches, C)
     queues = [[(pc, l) for pc, l in tagged if l[5] == s] for s in range(2 * C)]
     npieces = tagged[-1][0] + 1
+    # lane_done[l][pc]: number of launches of lane l belonging to pieces <= pc
     lane_upto = [[sum(1 for p, _ in queues[l] if p <= pc) for pc in range(npieces)] for l in range(C)]
-    # position in lane l's queue right AFTER its launch (piece pc, tag bit, level s); absent launches (empty ranges) need nothing
-    after = {}
-    for l in range(C):
-        for n, (pc, ln) in enumerate(queues[l]):
-            for bit in (1, 2):
-                if ln[7] & bit:
-                    after[(l, pc, bit, ln[0])] = n + 1
     pos = [0] * (2 * C)
     level = np.zeros((nx, ny), dtype=np.int16)
     rng = np.random.default_rng(seed)
-    total, done = len(launches), 0
+    total = len(launches)
+    done = 0
     while done < total:
         ready = []
         for s in range(2 * C):
             if pos[s] >= len(queues[s]):
                 continue
             pc, l = queues[s][pos[s]]
-            if s >= C:
-                b, lv = s - C, l[0]
-                if pc < npieces - 1:                     # coarse rule
-                    if pos[b] < lane_upto[b][pc] or pos[(b + 1) % C] < lane_upto[(b + 1) % C][pc]:
-                        continue
-                elif lv > 0:                            # fine rule on the last column piece
-                    need_b = after.get((b, pc, 2, lv - 1), 0)
-                    need_n = after.get(((b + 1) % C, pc, 1, lv - 1), 0)
-                    if pos[b] < need_b or pos[(b + 1) % C] < need_n:
-                        continue
+            if s >= C:                                  # chain of boundary b: lanes b and b+1 have finished piece pc
+                b = s - C
+                if pos[b] < lane_upto[b][pc] or pos[(b + 1) % C] < lane_upto[(b + 1) % C][pc]:
+                    continue
             ready.append(s)
         assert ready, "deadlock"
         s = int(rng.choice(ready))
-        pc, (lv, r0, r1, j0, j1, _, _, _) = queues[s][pos[s]]
+        pc, (lv, r0, r1, j0, j1, _, _) = queues[s][pos[s]]
         if j0 == j1 == 0:
             j1 = ny
         rws, cls = np.arange(r0, r1) % nx, np.arange(j0, j1) % ny
