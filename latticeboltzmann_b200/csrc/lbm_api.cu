@@ -661,9 +661,9 @@ void tb_plan(TbPlan *pl, int nx, int ny, int ldy, int strips_ok, int multi, int 
 		W += G * k;
 		budget = 60e6;
 	}
-	/* several concurrent chains share the L2: measured best per chain at 8192x32768 with two chains: 24-30 MB, DP and SP
-	 * (profiles/r02_run7 chain_sweep.log, r02_run8 chain_sweep_sp.log) */
-	if (chains > 1) budget = 54e6 / chains;
+	/* several concurrent chains share the L2: measured best per chain at 8192x32768 with two chains: 30 MB DP, 24-30 MB SP
+	 * (profiles/r02_run7 and r02_run10 chain_sweep.log, r02_run8 chain_sweep_sp.log) */
+	if (chains > 1) budget = (sizeof(real_t) == 8 ? 60e6 : 54e6) / chains;
 	if (2 * k + 2 + 2 * edge > nx) {                             /* (slabs, lanes) no room for the row pyramid */
 		pl->rows.n = nx; pl->rows.g = 1; pl->rows.e = 0; pl->rows.npieces = 1;
 		pl->rows.piece[0] = TbPiece{TB_WHOLE, 0, nx};
