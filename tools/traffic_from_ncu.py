@@ -2,6 +2,7 @@
 of tools/profile_target.py  ->  one entry of profiles/traffic.json:
 
     python tools/traffic_from_ncu.py launches.csv <key> <prec> <nx> <ny> <nsteps> [kernel-substring] >> (merged into profiles/traffic.json)
+    python tools/traffic_from_ncu.py --summary launches.csv out.summary.csv        (per-kernel table)
 
 dram_bytes_per_algorithmic_byte = sum of DRAM bytes over ALL step-kernel launches of the run / (18 reals x sites x timesteps):
 the capture must cover whole macro-steps (profile_target's nsteps a multiple of tb_depth, -c large enough)."""
@@ -28,7 +29,27 @@ def parse(path, needle):
     return list(rows.values())
 
 
+def summary(path, out):
+    """per-kernel table of a launch list: launches, time, DRAM bytes (what profiles/*/launches_*.summary.csv hold)"""
+    ls = parse(path, "")
+    tab = {}
+    for d in ls:
+        name = d["name"].split("(")[0]
+        t = tab.setdefault(name, [0, 0.0, 0.0, 0.0])
+        t[0] += 1
+        t[1] += d.get("gpu__time_duration.sum", 0) / 1e3
+        t[2] += d.get("dram__bytes_read.sum", 0) / 1e6
+        t[3] += d.get("dram__bytes_write.sum", 0) / 1e6
+    total = sum(t[1] for t in tab.values()) or 1.0
+    with open(out, "w") as fh:
+        fh.write("kernel,launches,total_time_us,avg_time_us,dram_read_MB,dram_write_MB,share_of_time\n")
+        for name, t in tab.items():
+            fh.write(f'"{name}",{t[0]},{t[1]:.1f},{t[1] / t[0]:.2f},{t[2]:.1f},{t[3]:.1f},{t[1] / total:.4f}\n')
+
+
 def main():
+    if sys.argv[1] == "--summary":
+        return summary(sys.argv[2], sys.argv[3])
     path, key, prec, nx, ny, nsteps = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6])
     needle = sys.argv[7] if len(sys.argv) > 7 else "stream_collide"
     ls = parse(path, needle)
