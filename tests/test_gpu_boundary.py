@@ -79,7 +79,9 @@ def test_boundary_options_match_oracle(prec, isa, nx, ny, outflow, slip):
             Lattice(nx, ny, prec, vecwidth=vw, outflow=True, inplace=True)
         return
     for tune in (dict(), dict(tb_depth=4, tb_rows=5), dict(tb_depth=6, tb_rows=7, tb_cols=64, pdl=1), dict(vec=1, tb_depth=2, hints=1),
-                 dict(vec=min(2, max(vw, 1)), tb_depth=4, tb_rows=3, tb_cols=16)):
+                 dict(vec=min(2, max(vw, 1)), tb_depth=4, tb_rows=3, tb_cols=16),
+                 # concurrent tile chains (lanes on their own streams): the open ends and the slip walls across lane boundaries
+                 dict(tb_depth=4, tb_rows=3, tb_chains=2), dict(tb_depth=2, tb_rows=2, tb_cols=32, tb_chains=3, pdl=1)):
         with Lattice(nx, ny, prec, vecwidth=vw, outflow=outflow, inplace=True) as lat:
             lat.set_tuning(**tune)
             lat.upload(fA, walls)
