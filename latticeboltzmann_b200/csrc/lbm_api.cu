@@ -288,6 +288,10 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 		c->tune.tb_depth = 16;                                   /* SP since its kernels run at 64 registers: 104.4 (k 16) vs 102.1 (k 8), r01_run28 */
 		c->tune.vec = sizeof(real_t) == 8 ? 1 : 4;
 		c->tune.tb_chains = 2;                                   /* two concurrent tile chains: DP 57.4 -> 65.6 GLUPS, SP 102.2 -> 119.5 (profiles/r02_run6) */
+		/* L2 eviction priorities (last level evict-first, the others evict-last): DP +1.8 % in 1000-timestep runs under the power
+		 * cap (profiles/r02_run11 long_hints.log), +0.1-0.8 % in short ones; SP -1.6 to -2.6 %, and DP -6 % on the small
+		 * lattices below (profiles/r02_run7): on for DP here only */
+		if (sizeof(real_t) == 8) c->tune.hints = 3;
 	}
 	if (c->inplace && (unsigned long long)c->nxl * c->ny <= (16ull << 20)) {
 		/* in-place small lattices (profiles/r01_run8, r01_run9): PDL + graph replay for both precisions; lattices
