@@ -222,7 +222,8 @@ typedef struct {
 	int hints;        /* bit 0: A/B kernel: L1::no_allocate loads + streaming stores; in-place kernels under temporal blocking: the
 	                     LAST level of a macro-step stores with the L2 evict-first policy (its results are not read again
 	                     while the tile is L2-resident).  bit 1 (in-place contexts): the other levels load and store with the
-	                     evict-last policy.  0 = default caching; measured neutral, never changes results */
+	                     evict-last policy.  Never changes results.  Default 3 for DP in-place lattices above 16 Mi sites (half
+	                     the DRAM traffic, +1.8 % in long runs), 0 elsewhere (SP and the small lattices lose 2-6 % with it) */
 	int pdl;          /* 1: step kernels are launched with programmatic dependent launch, so the next
 	                     step's CTAs are resident (waiting in griddepcontrol.wait) while this one drains */
 	int graph;        /* >0: steps are replayed from a captured CUDA graph of `graph` step pairs (single-slab contexts) */
