@@ -152,6 +152,16 @@ int lbm_compute_reynolds(lbm_ctx *ctx, real_t *re);
  * (LB.c:533-540); a multi-slab caller concatenates them in row order and finishes with
  * lbm_reynolds_from_column. */
 int lbm_reynolds_column(lbm_ctx *ctx, real_t *uy, char *is_fluid);
+/* The same column, for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Calls no cudaMalloc / cudaFree /
+ * cudaMallocAsync and no allocating library routine; the device scratch that lbm_reynolds_column allocates is a static device
+ * array inside the library here (LBM_STATIC_MAX_ROWS entries of u_y + fluid flags: 576 KB DP / 320 KB SP, held by every GPU that
+ * loads the library until exit).  Contexts with more than LBM_STATIC_MAX_ROWS local rows are refused with LBM_ERR_ARG.  Output
+ * identical to lbm_reynolds_column's, bit for bit.  All contexts on one GPU SHARE the array, and it keeps the previous call's
+ * contents (every entry that is read back is written first, nothing needs clearing): calls that overlap on the same GPU -- two
+ * host threads, two contexts -- race; serialise them.  Synchronises like lbm_reynolds_column. */
+#define LBM_STATIC_MAX_ROWS 65536
+int lbm_reynolds_column_static(lbm_ctx *ctx, real_t *uy, char *is_fluid);
 real_t lbm_reynolds_from_column(const real_t *uy, const char *is_fluid, int nx, real_t tau);
 /* rho, u_x, u_y of every site of buffer A in the order of PrintLattice (LB.c:621-629);
  * outputs are dense [nx_local][ny]; any may be NULL. */

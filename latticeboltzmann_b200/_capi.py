@@ -58,7 +58,7 @@ SYMBOLS = [
     "lbm_sizeof_real", "lbm_last_error", "lbm_version", "lbm_create", "lbm_destroy",
     "lbm_scene_reference", "lbm_initialize_arrays", "lbm_upload", "lbm_download", "lbm_upload_slab", "lbm_download_slab", "lbm_download_window", "lbm_set_walls", "lbm_load_walls",
     "lbm_do_timestep", "lbm_run", "lbm_run_timed", "lbm_apply_source", "lbm_stream_collide", "lbm_sync",
-    "lbm_compute_reynolds", "lbm_reynolds_column", "lbm_reynolds_from_column", "lbm_macroscopic",
+    "lbm_compute_reynolds", "lbm_reynolds_column", "lbm_reynolds_column_static", "lbm_reynolds_from_column", "lbm_macroscopic",
     "lbm_print_lattice", "lbm_print_lattice_group", "lbm_checksum", "lbm_check_finite", "lbm_slab_info_get", "lbm_ipc_export", "lbm_ipc_connect", "lbm_connect_local",
     "lbm_group_run", "lbm_halo_pack", "lbm_halo_unpack", "lbm_step_rows", "lbm_stream_handle",
     "lbm_stream_join", "lbm_set_tuning", "lbm_get_tuning", "lbm_kernel_launches", "lbm_tb_schedule", "lbm_tb_schedule_chains",
@@ -104,7 +104,7 @@ class Lib:
             "lbm_set_walls": [vp, vp, ci], "lbm_load_walls": [vp, ctypes.c_char_p],
             "lbm_do_timestep": [vp], "lbm_run": [vp, ci], "lbm_run_timed": [vp, ci, ctypes.POINTER(ctypes.c_float)],
             "lbm_apply_source": [vp, ci], "lbm_stream_collide": [vp, ci], "lbm_sync": [vp],
-            "lbm_compute_reynolds": [vp, ctypes.POINTER(self.real)], "lbm_reynolds_column": [vp, vp, vp],
+            "lbm_compute_reynolds": [vp, ctypes.POINTER(self.real)], "lbm_reynolds_column": [vp, vp, vp], "lbm_reynolds_column_static": [vp, vp, vp],
             "lbm_macroscopic": [vp, vp, vp, vp], "lbm_print_lattice": [vp, ctypes.c_char_p],
             "lbm_checksum": [vp, ci, ctypes.POINTER(ctypes.c_ulonglong)], "lbm_check_finite": [vp, ctypes.POINTER(ctypes.c_ulonglong)],
             "lbm_slab_info_get": [vp, ctypes.POINTER(self.SlabInfo)], "lbm_ipc_export": [vp, vp],

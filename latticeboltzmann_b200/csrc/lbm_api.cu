@@ -1276,6 +1276,53 @@ int lbm_reynolds_column(lbm_ctx *c, real_t *uy, char *is_fluid)
 	return LBM_OK;
 }
 
+/* ---- lbm_reynolds_column without any allocation (include/lbm_b200.h) ----
+ * The scratch lbm_reynolds_column takes from cudaMallocAsync lives here in a file-scope device array instead: LBM_STATIC_MAX_ROWS
+ * values of u_y followed by as many fluid flags (576 KB in the DP library, 320 KB in the SP one), held by every GPU that loads
+ * the library until the process exits.  In host code `g_static_scratch` is only a stand-in for the symbol, NOT a device address:
+ * the address is asked for once per device, with that device current (cudaGetSymbolAddress), and that pointer goes to the kernel. */
+static __device__ __align__(256) unsigned char g_static_scratch[(size_t)LBM_STATIC_MAX_ROWS * (sizeof(real_t) + 1)];
+
+static int static_scratch_address(const lbm_ctx *c, unsigned char **out)
+{
+	static unsigned char *cached[64] = {nullptr};                /* per device; racing first calls store the same value */
+	const int dev = c->cfg.device;
+	if (dev < 0 || dev >= 64) return fail(LBM_ERR_ARG, "lbm_reynolds_column_static: device %d", dev);
+	if (!cached[dev]) {
+		void *ptr = nullptr;
+		cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);   /* the caller made c's device current (set_device) */
+		if (e != cudaSuccess || !ptr) return fail(LBM_ERR_CUDA, "lbm_reynolds_column_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+		cached[dev] = (unsigned char *)ptr;
+	}
+	*out = cached[dev];
+	return LBM_OK;
+}
+
+int lbm_reynolds_column_static(lbm_ctx *c, real_t *uy, char *is_fluid)
+{
+	if (!c || !uy || !is_fluid) return fail(LBM_ERR_ARG, "lbm_reynolds_column_static: null argument");
+	if (c->nxl > LBM_STATIC_MAX_ROWS)
+		return fail(LBM_ERR_ARG, "lbm_reynolds_column_static: %d local rows exceed the static scratch of LBM_STATIC_MAX_ROWS = %d rows "
+		                         "(use lbm_reynolds_column)", c->nxl, LBM_STATIC_MAX_ROWS);
+	if (!c->has_state) return fail(LBM_ERR_STATE, "lbm_reynolds_column_static: no lattice loaded");
+	int rc;
+	if ((rc = lbm_sync(c))) return rc;                           /* sets the device; no allocation */
+	unsigned char *scratch = nullptr;
+	if ((rc = static_scratch_address(c, &scratch))) return rc;
+	real_t *duy = (real_t *)scratch;
+	char *dfl = (char *)(scratch + (size_t)LBM_STATIC_MAX_ROWS * sizeof(real_t));
+	cudaStream_t st = c->stream[0];
+	const int jc = (int)((real_t)c->ny / 2.0);                  /* LB.c:527 */
+	/* nothing in the scratch has to start at zero: the kernel writes every entry [0, nxl) that is copied out below */
+	reynolds_column_static_kernel<real_t><<<(c->nxl + 127) / 128, 128, 0, st>>>(c->f[0], c->plane, c->ldy, c->nxl, jc, c->mask, c->ldw, duy, dfl);
+	CK(cudaGetLastError());
+	c->launches++;
+	CK(cudaMemcpyAsync(uy, duy, (size_t)c->nxl * sizeof(real_t), cudaMemcpyDeviceToHost, st));
+	CK(cudaMemcpyAsync(is_fluid, dfl, (size_t)c->nxl, cudaMemcpyDeviceToHost, st));
+	CK(cudaStreamSynchronize(st));
+	return LBM_OK;
+}
+
 /* the serial accumulation and the final scaling of ComputeReynolds, LB.c:529-546 */
 real_t lbm_reynolds_from_column(const real_t *uy, const char *is_fluid, int nx, real_t tau)
 {

@@ -1048,6 +1048,23 @@ __global__ void macroscopic_kernel(const T *f, size_t plane, int ldy, int nxl, i
 	if (uy_o) uy_o[g] = A::div(A::sub(A::add(A::add(v[5], v[1]), v[8]), A::add(A::add(v[6], v[3]), v[7])), rho);
 }
 
+// The centre column of macroscopic_kernel for lbm_reynolds_column_static: u_y of column jc in the same operation order, plus
+// the fluid flag of each site from the packed wall mask, both into caller-provided device memory (there: the static scratch).
+template <typename T>
+__global__ void reynolds_column_static_kernel(const T *f, size_t plane, int ldy, int nxl, int jc, const uint32_t *mask, int ldw,
+                                              T *uy_o, char *fluid_o)
+{
+	typedef fp<T> A;
+	const int r = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+	if (r >= nxl) return;
+	const T *site = f + (size_t)(r + 1) * ldy + jc;
+	T v[9], rho = T(0);
+#pragma unroll
+	for (int s = 0; s < 9; s++) { v[s] = site[(size_t)s * plane]; rho = A::add(rho, v[s]); }
+	uy_o[r] = A::div(A::sub(A::add(A::add(v[5], v[1]), v[8]), A::add(A::add(v[6], v[3]), v[7])), rho);
+	fluid_o[r] = (char)(((mask[(size_t)r * ldw + (jc >> 5)] >> (jc & 31)) & 1u) == 0u);
+}
+
 // ---- neighbour barrier between ranks living in different processes / GPUs ----
 // signal: my epoch into the slot each neighbour reserves for me.  Runs after the boundary
 // kernel in stream order, so the halo stores it announces have been performed.

@@ -157,6 +157,14 @@ class Lattice:
         self._call("lbm_reynolds_column", _ptr(uy), _ptr(fluid))
         return uy, fluid
 
+    def reynolds_column_static(self, uy=None, fluid=None):
+        """lbm_reynolds_column_static: the same column without any allocation on the library's side (static device scratch,
+        at most LBM_STATIC_MAX_ROWS local rows); pass ``uy`` / ``fluid`` to reuse the caller's buffers."""
+        uy = np.zeros(self.nx_local, dtype=self.dtype) if uy is None else uy
+        fluid = np.zeros(self.nx_local, dtype=np.int8) if fluid is None else fluid
+        self._call("lbm_reynolds_column_static", _ptr(uy), _ptr(fluid))
+        return uy, fluid
+
     def reynolds_from_column(self, uy, fluid):
         uy = np.ascontiguousarray(uy, dtype=self.dtype)
         fluid = np.ascontiguousarray(fluid, dtype=np.int8)
