@@ -596,9 +596,9 @@ def bench_multi(args):
                 "config": {"workload": headline_workload(world), "lattice": f"{nx}x{ny}", "timesteps_per_step": T,
                            "scene": "channel walls + disc obstacle (InitializeArrays closed form), tau 0.7, accel 0.005",
                            "parallelism": f"row slabs x{world}, halo rows stored peer-to-peer over NVLink ({args.transport}), seam chain on a second stream",
-                           "engine": ("in-place single buffer per slab (AA kernels) + 2-D temporal blocking in L2 across the slab seams (library defaults)"
+                           "engine": ("in-place single buffer per slab (AA kernels) + 2-D temporal blocking in L2 across the slab seams, two concurrent tile chains per slab (library defaults)"
                                       if inplace else "A/B double buffer per slab, one pull kernel per timestep (HBM-bound)"),
-                           "l2": "19.3 GB per GPU, far larger than L2; nothing is flushed: L2 residency of the ~60 MB tiles for 16 timesteps is the engine",
+                           "l2": "19.3 GB per GPU, far larger than L2; nothing is flushed: L2 residency of two ~30 MB tiles for 16 timesteps is the engine",
                            "parity": ("bit-exact: " if ok else "NOT CLEAN: ") + ("; ".join(parity) if parity else "skipped (--no-parity)"),
                            "skipped": skipped},
                 "roofline": dp["roofline"], "e2e": dp["e2e"], "gpu_launches": dp["launches"], "clocks": clocks,
