@@ -225,10 +225,10 @@ int lbm_stream_join(lbm_ctx *ctx);   /* main stream waits for the boundary strea
 /* ---- tuning / accounting ---- */
 /* What round 1 measured and dropped (persistent kernel, dataflow kernel, fused step pairs, warp-shuffle neighbours, software
  * pipelining, capped grids: all slower than the defaults, numbers in DESIGN.md / profiles/) is no longer here; the
- * shared-memory staged kernels (cp.async / TMA) live in the experiment build only (include/lbm_b200_experimental.h). */
+ * shared-memory staged kernels (cp.async / TMA) and the CTA size knob (128 threads measured best at every size, profiles/r01_run2)
+ * live in the experiment build only (include/lbm_b200_experimental.h). */
 typedef struct {
 	int vec;          /* sites per thread: 1, 2 or 4; 0 = by lattice size (DP: 1 up to 16 Mi sites and in place, else 4; SP: 4) */
-	int block;        /* threads per CTA; 0 = default 128 (the SP in-place kernels run at most 256) */
 	int hints;        /* bit 0: A/B kernel: L1::no_allocate loads + streaming stores; in-place kernels under temporal blocking: the
 	                     LAST level of a macro-step stores with the L2 evict-first policy (its results are not read again
 	                     while the tile is L2-resident).  bit 1 (in-place contexts): the other levels load and store with the

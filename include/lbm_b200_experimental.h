@@ -19,6 +19,8 @@ extern "C" {
 typedef struct {
 	int stage_smem;       /* 0 off; 1 = cp.async staging in both phases; 2 = phase 2 by TMA bulk copies (phase 1: cp.async) */
 	int rows_per_thread;  /* >= 2: rows each thread walks (the staging pipelines over them); vec must be 1 */
+	int block;            /* threads per CTA of the step kernels: 32..512, a multiple of 32; 0 = the product's 128 (the SP in-place kernels run
+	                         at most 256) */
 	int smem_pad;         /* bytes of (unused) dynamic shared memory requested by every in-place step launch: caps the CTAs
 	                         resident per SM -- the residency probe (a CTA's lifetime is what one launch loses at its drain) */
 } lbm_experimental;

@@ -43,12 +43,12 @@ def _structs(real):
                     ("dev_f", ctypes.c_void_p * 2), ("dev_flags", ctypes.c_void_p)]
 
     class Tuning(ctypes.Structure):
-        _fields_ = [("vec", ctypes.c_int), ("block", ctypes.c_int), ("hints", ctypes.c_int), ("pdl", ctypes.c_int),
+        _fields_ = [("vec", ctypes.c_int), ("hints", ctypes.c_int), ("pdl", ctypes.c_int),
                     ("graph", ctypes.c_int), ("tb_depth", ctypes.c_int), ("tb_rows", ctypes.c_int), ("tb_cols", ctypes.c_int),
                     ("tb_chains", ctypes.c_int)]
 
     class Experimental(ctypes.Structure):      # include/lbm_b200_experimental.h (experiment build only)
-        _fields_ = [("stage_smem", ctypes.c_int), ("rows_per_thread", ctypes.c_int), ("smem_pad", ctypes.c_int)]
+        _fields_ = [("stage_smem", ctypes.c_int), ("rows_per_thread", ctypes.c_int), ("block", ctypes.c_int), ("smem_pad", ctypes.c_int)]
 
     return Config, Scene, SlabInfo, Tuning, Experimental
 

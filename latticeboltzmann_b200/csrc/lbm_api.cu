@@ -273,7 +273,6 @@ int lbm_create(lbm_ctx **out, const lbm_config *cfg)
 
 	/* measured best on B200 at every size (profiles/r01_run2): direct neighbour loads, 128-thread CTAs */
 	c->tune.vec = default_vec(c);
-	c->tune.block = 128;
 	c->tune.hints = 0;
 	/* small DP lattices are launch-bound (a step is ~35 us): PDL + graph replay of 10 step pairs measured
 	 * 43.7 vs 41.1 GLUPS at 400x4000 (profiles/r01_run3); no gain for SP or for large lattices */
@@ -403,7 +402,8 @@ int sm_count(int device)
 cudaError_t launch_staged(lbm_ctx *c, int phase, const StepParams<real_t> &p, unsigned rows, unsigned ncols, bool whole_rows, cudaStream_t st, int pdl)
 {
 	if (!c->exp.stage_smem || c->exp.rows_per_thread < 2 || c->nyvec != c->ny || c->outflow) return cudaErrorNotYetImplemented;
-	unsigned blk = (unsigned)c->tune.block > 256u ? 256u : (unsigned)c->tune.block;
+	unsigned blk = c->exp.block ? (unsigned)c->exp.block : 128u;
+	if (blk > 256u) blk = 256u;
 	unsigned gy = (rows + (unsigned)c->exp.rows_per_thread - 1) / (unsigned)c->exp.rows_per_thread;
 	if (gy > 65535u) gy = 65535u;
 	if (phase == 2 && c->exp.stage_smem == 2 && whole_rows && ((size_t)c->ny * sizeof(real_t)) % 16 == 0) {   /* TMA both ways; whole rows of 16-byte units */
@@ -462,7 +462,10 @@ int launch_step(lbm_ctx *c, int src, int r0, int r1, int tail_source, cudaStream
 	if (c->vw > 1 && c->nyvec > 0) {
 		int V = c->tune.vec;
 		if (V > c->vw) V = c->vw;
-		unsigned block = (unsigned)c->tune.block;
+		unsigned block = 128;                                    /* measured best at every size (profiles/r01_run2) */
+#ifdef LBM_EXPERIMENTAL
+		if (c->exp.block) block = (unsigned)c->exp.block;
+#endif
 		if (c->inplace && sizeof(real_t) == 4 && block > 256) block = 256;      /* launch bounds of the SP in-place kernels */
 		/* PDL only where consecutive step kernels follow each other on one stream with nothing between */
 		const int pdl = c->tune.pdl && (c->sync_mode == SYNC_SELF || c->in_wavefront) && c->nyvec == c->ny;
@@ -1466,9 +1469,7 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 	if (!c || !t) return fail(LBM_ERR_ARG, "lbm_set_tuning: null argument");
 	lbm_tuning n = *t;
 	if (n.vec == 0) n.vec = default_vec(c);
-	if (n.block == 0) n.block = 128;
 	if (n.vec != 1 && n.vec != 2 && n.vec != 4) return fail(LBM_ERR_ARG, "lbm_set_tuning: vec %d", n.vec);
-	if (n.block < 32 || n.block > 512 || (n.block & 31)) return fail(LBM_ERR_ARG, "lbm_set_tuning: block %d", n.block);
 	if (n.hints < 0 || n.hints > 3 || (n.hints > 1 && !c->inplace)) return fail(LBM_ERR_ARG, "lbm_set_tuning: hints %d", n.hints);
 	if (n.pdl < 0 || n.pdl > 1) return fail(LBM_ERR_ARG, "lbm_set_tuning: pdl %d", n.pdl);
 	if (n.graph < 0 || n.graph > 1000) return fail(LBM_ERR_ARG, "lbm_set_tuning: graph %d", n.graph);
@@ -1486,7 +1487,8 @@ int lbm_set_tuning(lbm_ctx *c, const lbm_tuning *t)
 int lbm_set_experimental(lbm_ctx *c, const lbm_experimental *x)
 {
 	if (!c || !x) return fail(LBM_ERR_ARG, "lbm_set_experimental: null argument");
-	if (x->stage_smem < 0 || x->stage_smem > 2 || x->rows_per_thread < 0 || x->rows_per_thread > 1024 || x->smem_pad < 0 || x->smem_pad > 48 * 1024) return fail(LBM_ERR_ARG, "lbm_set_experimental: stage_smem %d, rows_per_thread %d", x->stage_smem, x->rows_per_thread);
+	if (x->stage_smem < 0 || x->stage_smem > 2 || x->rows_per_thread < 0 || x->rows_per_thread > 1024 || x->smem_pad < 0 || x->smem_pad > 48 * 1024 ||
+	    (x->block != 0 && (x->block < 32 || x->block > 512 || (x->block & 31)))) return fail(LBM_ERR_ARG, "lbm_set_experimental: stage_smem %d, rows_per_thread %d", x->stage_smem, x->rows_per_thread);
 	drop_graph(c);
 	c->exp = *x;
 	return LBM_OK;

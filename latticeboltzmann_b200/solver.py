@@ -218,7 +218,7 @@ class Lattice:
         self._call("lbm_set_tuning", ctypes.byref(t))
 
     def set_experimental(self, **kw):
-        """Experiment build only (include/lbm_b200_experimental.h): stage_smem, rows_per_thread, smem_pad."""
+        """Experiment build only (include/lbm_b200_experimental.h): stage_smem, rows_per_thread, block, smem_pad."""
         x = self.lib.Experimental(**kw)
         self._call("lbm_set_experimental", ctypes.byref(x))
 

@@ -130,10 +130,8 @@ def _variants(prec):
     out = []
     for v in vecs:
         for hints in (0, 1):
-            out.append(dict(vec=v, hints=hints, block=256))
-    out += [dict(vec=vecs[-1], hints=0, block=128), dict(vec=2, hints=1, block=512), dict(vec=2, hints=0, block=64),
-            dict(vec=1, hints=0, block=128, pdl=1, graph=2), dict(vec=vecs[-1], hints=1, block=256, pdl=1, graph=0),
-            dict(vec=2, hints=0, block=128, pdl=0, graph=1)]
+            out.append(dict(vec=v, hints=hints))
+    out += [dict(vec=1, hints=0, pdl=1, graph=2), dict(vec=vecs[-1], hints=1, pdl=1, graph=0), dict(vec=2, hints=0, pdl=0, graph=1)]
     return out
 
 
@@ -153,8 +151,7 @@ def test_every_kernel_variant_is_bit_identical(prec):
     vecs = (1, 2, 4)
     with _lattice(c, inplace=True) as lat:
         for v in vecs:
-            for extra in (dict(block=128), dict(block=256), dict(block=64, pdl=1, graph=2), dict(block=512, pdl=1), dict(block=96),
-                          dict(block=32, tb_depth=4, tb_rows=11, tb_cols=40), dict(block=128, hints=1, tb_depth=2, tb_rows=30)):
+            for extra in (dict(), dict(pdl=1, graph=2), dict(pdl=1), dict(tb_depth=4, tb_rows=11, tb_cols=40), dict(hints=1, tb_depth=2, tb_rows=30)):
                 tune = dict(dict(vec=v, hints=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0), **extra)
                 lat.set_tuning(**tune)
                 lat.upload(fA, walls)
@@ -165,7 +162,7 @@ def test_every_kernel_variant_is_bit_identical(prec):
         # evict-first stores on the last level
         for k, h, g, w in ((2, 0, 0, 0), (4, 7, 0, 0), (8, 16, 1, 0), (46, 3, 0, 0), (10, 200, 1, 0), (4, 1, 1, 0), (6, 90, 0, 0),
                            (4, 20, 0, 128), (6, 0, 1, 104), (2, 7, 0, 64), (8, 30, 1, 8), (16, 40, 0, 200), (2, 95, 1, 256)):
-            tune = dict(vec=vecs[-1] if w == 0 else vecs[(k // 2) % len(vecs)], hints=(k // 2) & 1, block=128,
+            tune = dict(vec=vecs[-1] if w == 0 else vecs[(k // 2) % len(vecs)], hints=(k // 2) & 1,
                         pdl=g, graph=g, tb_depth=k, tb_rows=h, tb_cols=w)
             lat.set_tuning(**tune)
             lat.upload(fA, walls)
@@ -191,9 +188,10 @@ def test_staged_kernel_is_bit_identical(prec):
                                  # 2: phase 2 through TMA bulk copies (whole rows), phase 1 through cp.async
                                  (2, 2, {}), (3, 2, dict(tb_depth=4, tb_rows=9, pdl=1)), (96, 2, dict(block=64)),
                                  (7, 2, dict(block=32, pdl=1, graph=2)), (4, 2, dict(tb_depth=4, tb_rows=20, tb_cols=128))):
-            tune = dict(dict(vec=1, hints=0, block=128, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0), **extra)
+            tune = dict(dict(vec=1, hints=0, pdl=0, graph=0, tb_depth=0, tb_rows=0, tb_cols=0), **extra)
+            blk = tune.pop("block", 0)                        # the CTA size is a knob of the experiment build
             lat.set_tuning(**tune)
-            lat.set_experimental(stage_smem=mode, rows_per_thread=rpt)
+            lat.set_experimental(stage_smem=mode, rows_per_thread=rpt, block=blk)
             lat.upload(fA, walls)
             l0 = lat.launches
             lat.run(4)

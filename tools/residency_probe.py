@@ -20,8 +20,8 @@ for prec in precs:
             for block in (64, 128, 256):
                 for pad in (0, 24 << 10, 28 << 10, 32 << 10, 37 << 10, 45 << 10, 48 << 10):
                     per_sm = min(2048 // block, 32, 228 * 1024 // (pad + 1024)) if pad else None
-                    lat.set_tuning(**{**base, "block": block})
-                    lat.set_experimental(stage_smem=0, rows_per_thread=0, smem_pad=pad)
+                    lat.set_tuning(**base)
+                    lat.set_experimental(stage_smem=0, rows_per_thread=0, block=block, smem_pad=pad)
                     lat.run_timed(200)
                     ms = min(lat.run_timed(2000) for _ in range(2))
                     rec = dict(prec=prec, nx=nx, ny=ny, block=block, smem_pad=pad, ctas_per_sm_cap=per_sm, mlups=round(nx * ny * 2000 / ms / 1e3, 1))

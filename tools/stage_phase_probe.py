@@ -36,8 +36,8 @@ for prec, nx, ny in (("dp", 400, 2000), ("sp", 400, 4000)):
             for rpt in (4, 8, 16, 32):
                 combos.append(dict(vec=1, rows_per_thread=rpt, stage_smem=2, block=blk))
         for cmb in combos:
-            lat.set_tuning(pdl=1, graph=0, tb_depth=0, vec=cmb['vec'], block=cmb['block'])
-            lat.set_experimental(stage_smem=cmb['stage_smem'], rows_per_thread=cmb['rows_per_thread'])
+            lat.set_tuning(pdl=1, graph=0, tb_depth=0, vec=cmb['vec'])
+            lat.set_experimental(stage_smem=cmb['stage_smem'], rows_per_thread=cmb['rows_per_thread'], block=cmb['block'])
             for phase in (0, 1):
                 if cmb["stage_smem"] == 2 and phase == 0:
                     continue

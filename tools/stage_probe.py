@@ -27,8 +27,8 @@ for prec, nx, ny, T in (("dp", 400, 2000, 4000), ("dp", 400, 4000, 2000), ("sp",
         init(); lat.run(32); want = lat.download("A")
         for mode, blk in ((1, 128), (1, 256), (2, 128), (2, 64)):     # 1: cp.async both phases; 2: TMA bulk copies in phase 2
             for rpt in (4, 8, 16):
-                lat.set_tuning(vec=1, block=blk)
-                lat.set_experimental(stage_smem=mode, rows_per_thread=rpt)
+                lat.set_tuning(vec=1)
+                lat.set_experimental(stage_smem=mode, rows_per_thread=rpt, block=blk)
                 init(); lat.run(32)
                 same = bool(np.array_equal(lat.download("A").view(np.uint8), want.view(np.uint8)))
                 lat.run_timed(min(T, 400))

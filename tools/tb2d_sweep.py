@@ -30,7 +30,7 @@ for prec in precs:
                             combos.append((k, h, w, vec, g))
         for k, h, w, vec, g in combos:
             T = 48
-            lat.set_tuning(vec=vec, hints=0, block=128, pdl=1 if k else 0, graph=g,
+            lat.set_tuning(vec=vec, hints=0, pdl=1 if k else 0, graph=g,
                            tb_depth=k, tb_rows=h, tb_cols=w)
             lat.run_timed(max(k, 2))
             l0 = lat.launches

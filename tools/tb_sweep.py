@@ -35,7 +35,7 @@ def main():
                 for vec in vecs:
                     for k, h in combos:
                         for g in ((1,) if nx <= 800 else (0, 1)):
-                            lat.set_tuning(vec=vec, hints=0, block=128, pdl=1 if nx <= 800 else g,
+                            lat.set_tuning(vec=vec, hints=0, pdl=1 if nx <= 800 else g,
                                            graph=10 * g, tb_depth=k, tb_rows=h)
                             lat.run_timed(max(2 * k, T // 10) & ~1)
                             l0 = lat.launches
