@@ -243,7 +243,8 @@ typedef struct {
 	                     is L2-resident, so HBM sees each site once per tb_depth steps instead of every step.
 	                     Possible because the in-place kernels have no write-after-read hazards: a row may take
 	                     step t as soon as rows i-1, i, i+1 have taken step t-1.  0 = off (one launch per step). */
-	int tb_rows;      /* band height H in rows; 0 = chosen so that (H + tb_depth) rows take ~45 MB (DP) / 60 MB (SP) */
+	int tb_rows;      /* band height H in rows; 0 = chosen so that a tile of (H + tb_depth) rows takes its share of L2: one chain
+	                     45 MB (DP) / 60 MB (SP) in full-width bands, 60 MB in 2-D tiles; tb_chains = C: 60 MB (DP) / 54 MB (SP) / C */
 	int tb_cols;      /* column-strip width W of the 2-D schedule (multiple of 8): wide lattices are cut into strips as well
 	                     as bands, the tile (H + k) x (W + 8k) sites is what stays in L2.  0 = automatic (strips of 16 KB
 	                     row segments, 32 KB on slabs, only where full-width bands would be lower than 64 rows), >= ny = full-width rows */
